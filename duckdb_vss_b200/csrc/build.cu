@@ -1,0 +1,241 @@
+// K2/K3/K4 — bulk graph construction: one warp per inserted vector, many inserts in flight on the live graph.
+// Restates index_gt::add / update (usearch index.hpp:2297-2378, 2405-2463) = connect_node_across_levels_ (:3227-3244):
+// greedy descent (search_for_one_), per-level beam search (search_to_insert_, :3430-3496), the neighbour-selection
+// heuristic (refine_, :3602-3638; connect_new_node_, :3247-3267) and reverse links with re-pruning
+// (reconnect_neighbor_nodes_, :3270-3313), as driven by PhysicalCreateHNSWIndex (hnsw_index_physical_create.cpp:144-205).
+//
+// Concurrency model: the reference runs T host threads that take per-node spin locks while reading and writing
+// neighbour lists. Here thousands of warps play the threads. Lists are read WITHOUT locks (every 4-byte entry is
+// always a valid slot or the sentinel, so a torn read only yields a slightly stale list), and a node's lock is held
+// only while its list is rewritten; a warp never holds two locks, so there is no lock-order deadlock.
+// With one warp (concurrency 1) the kernel reproduces the reference's single-thread build byte for byte.
+#include "kernels.h"
+
+namespace gvss {
+
+__device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
+                                            const ScratchLayout &sl) {
+    w.mbar = reinterpret_cast<uint64_t *>(smem + sm.off_mbar);
+    w.stage[0] = reinterpret_cast<float *>(smem + sm.off_stage0);
+    w.stage[1] = reinterpret_cast<float *>(smem + sm.off_stage1);
+    w.c = reinterpret_cast<float *>(smem + sm.off_c);
+    w.q = reinterpret_cast<float *>(smem + sm.off_q);
+    w.heap = reinterpret_cast<Cand *>(smem + sm.off_heap);
+    w.top_d = reinterpret_cast<float *>(smem + sm.off_top_d);
+    w.top_s = reinterpret_cast<uint32_t *>(smem + sm.off_top_s);
+    w.rstride = sm.rstride;
+    w.heap_smem = sm.heap_smem;
+    uint8_t *base = scratch + (size_t)blockIdx.x * sl.bytes_per_warp;
+    w.vis = reinterpret_cast<uint32_t *>(base);
+    w.vis_mask = sl.vis_slots - 1;
+    w.vis_limit = sl.vis_limit;
+    w.heap_ovf = reinterpret_cast<Cand *>(base + (size_t)sl.vis_slots * 4);
+    w.heap_total = sm.heap_smem + sl.heap_ovf;
+    w.phase[0] = w.phase[1] = 0;
+    if (lane_id() == 0) {
+        mbar_init(&w.mbar[0], 1);
+        mbar_init(&w.mbar[1], 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ void lock_node(uint32_t *locks, uint32_t s) {
+    if (lane_id() == 0) {
+        while (atomicCAS(&locks[s], 0u, 1u) != 0u) __nanosleep(64);
+    }
+    __syncwarp();
+    __threadfence();
+}
+__device__ __forceinline__ void unlock_node(uint32_t *locks, uint32_t s) {
+    __threadfence();
+    __syncwarp();
+    if (lane_id() == 0) atomicExch(&locks[s], 0u);
+    __syncwarp();
+}
+
+// refine_ (index.hpp:3602-3638). Candidates = w.top_* [0, ncand) ascending. Keeps c iff for every already kept s:
+// !(d(c, s) < d(c, q)). Lanes hold 32 consecutive candidates; each kept node costs one batch of distances.
+template <int METRIC>
+__device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32_t ncand, uint32_t needed,
+                                           uint32_t *kept_s, float *kept_d, uint32_t &staged) {
+    const uint32_t lane = lane_id();
+    if (ncand < needed) {
+        for (uint32_t i = lane; i < ncand; i += 32) { kept_s[i] = w.top_s[i]; kept_d[i] = w.top_d[i]; }
+        __syncwarp();
+        return ncand;
+    }
+    uint32_t nkept = 0;
+    for (uint32_t base = 0; base < ncand && nkept < needed; base += 32) {
+        const uint32_t my = base + lane;
+        bool alive = my < ncand;
+        const uint32_t cs = alive ? w.top_s[my] : kInvalid;
+        const float cd = alive ? w.top_d[my] : 0.0f;
+        const uint32_t nprev = nkept;
+        for (uint32_t k = 0; k < nprev; k++) {
+            if (!__ballot_sync(kFull, alive)) break;
+            const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, kept_s[k]}, cs, alive, staged);
+            if (alive && d < cd) alive = false;
+        }
+        uint32_t amask = __ballot_sync(kFull, alive);
+        while (amask && nkept < needed) {
+            const uint32_t j = __ffs(amask) - 1;
+            const uint32_t sj = __shfl_sync(kFull, cs, j);
+            const float dj = __shfl_sync(kFull, cd, j);
+            if (lane == 0) { kept_s[nkept] = sj; kept_d[nkept] = dj; }
+            __syncwarp();
+            nkept++;
+            if (nkept == needed) break;
+            const bool act = alive && lane > j;
+            if (__ballot_sync(kFull, act)) {
+                const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, sj}, cs, act, staged);
+                if (act && d < cd) alive = false;
+            }
+            amask = __ballot_sync(kFull, alive && lane > j);
+        }
+    }
+    return nkept;
+}
+
+template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    WarpWs w;
+    carve_build(w, smem, p.sm, p.scratch, p.sl);
+    const uint32_t lane = lane_id();
+    const uint32_t cmax = max(g.M, g.M0);
+    uint32_t *mine_s = reinterpret_cast<uint32_t *>(smem + p.sm.off_misc);
+    uint32_t *kept_s = mine_s + (cmax + 1);
+    float *kept_d = reinterpret_cast<float *>(kept_s + (cmax + 1));
+    const uint32_t top_limit_all = p.sm.top_cap; // never reached: plain insert_reserved
+    uint32_t staged = kInvalid;
+
+    for (;;) {
+        unsigned long long idx = 0;
+        if (lane == 0) idx = atomicAdd(p.work_counter, 1ull);
+        idx = __shfl_sync(kFull, idx, 0);
+        if (idx >= p.end) break;
+        const uint32_t slot = p.slots[idx];
+        const int level = p.levels[slot];
+
+        for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = g.vectors[(size_t)slot * g.dpad + i];
+        __syncwarp();
+
+        unsigned long long es = 0;
+        if (lane == 0) {
+            es = __ldcg(p.entry_state);
+            if (es == ~0ull) { // first node of the graph: index.hpp:2352-2357
+                const unsigned long long mineEs = ((unsigned long long)(uint32_t)level << 32) | slot;
+                const unsigned long long old = atomicCAS(p.entry_state, ~0ull, mineEs);
+                es = (old == ~0ull) ? ~0ull : old;
+            }
+        }
+        es = __shfl_sync(kFull, es, 0);
+        if (es == ~0ull) continue;
+        const int max_level = (int)(es >> 32);
+        const uint32_t entry = (uint32_t)(es & 0xFFFFFFFFull);
+
+        Counters cnt = {0, 0, 0, 0};
+        uint32_t closest = greedy_descent<METRIC, true>(g, w, entry, max_level, level, cnt, staged);
+
+        for (int l = min(level, max_level); l >= 0; --l) {
+            uint32_t top_size = 0;
+            beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
+
+            // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)
+            const uint32_t cap_l = l ? g.M : g.M0;
+            uint32_t nk = refine<METRIC>(g, w, top_size, g.M, kept_s, kept_d, staged);
+            nk = min(nk, cap_l);
+            for (uint32_t i = lane; i < nk; i += 32) mine_s[i] = kept_s[i];
+            __syncwarp();
+            uint32_t capx;
+            uint32_t *mylist = list_ptr(g, slot, l, capx);
+            lock_node(p.locks, slot);
+            {
+                // the list is normally blank; links appended meanwhile by concurrent inserts are kept behind ours
+                uint32_t extra = kInvalid;
+                if (lane < capx) extra = __ldcg(mylist + lane);
+                bool keep_extra = extra != kInvalid;
+                for (uint32_t i = 0; i < nk; i++) if (extra == mine_s[i]) keep_extra = false;
+                const uint32_t emask = __ballot_sync(kFull, keep_extra);
+                const uint32_t epos = nk + __popc(emask & ((1u << lane) - 1u));
+                __syncwarp();
+                for (uint32_t i = lane; i < capx; i += 32) mylist[i] = i < nk ? mine_s[i] : kInvalid;
+                __syncwarp();
+                if (keep_extra && epos < capx) mylist[epos] = extra;
+            }
+            unlock_node(p.locks, slot);
+            closest = mine_s[0];
+
+            // reconnect_neighbor_nodes_
+            for (uint32_t i = 0; i < nk; i++) {
+                const uint32_t close = mine_s[i];
+                if (close == slot) continue;
+                uint32_t capc;
+                uint32_t *clist = list_ptr(g, close, l, capc);
+                lock_node(p.locks, close);
+                uint32_t cntc = 0;
+                bool present = false;
+                for (uint32_t base = 0; base < capc; base += 32) {
+                    const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
+                    cntc += __popc(__ballot_sync(kFull, e != kInvalid));
+                    present |= __ballot_sync(kFull, e == slot) != 0;
+                }
+                if (present) { unlock_node(p.locks, close); continue; }
+                if (cntc < capc) {
+                    if (lane == 0) clist[cntc] = slot;
+                    unlock_node(p.locks, close);
+                    continue;
+                }
+                // saturated: candidates = {(d(new, close), new)} ∪ {(d(close, x), x)}, then the heuristic with needed = cap
+                uint32_t tsz = 0;
+                float dn = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
+                dn = __shfl_sync(kFull, dn, 0);
+                top_insert(w, tsz, top_limit_all, dn, slot);
+                for (uint32_t base = 0; base < capc; base += 32) {
+                    const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
+                    const bool act = e != kInvalid;
+                    const uint32_t am = __ballot_sync(kFull, act);
+                    if (!am) break;
+                    const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, close}, e, act, staged);
+                    for (uint32_t m = am; m; m &= m - 1) {
+                        const uint32_t j = __ffs(m) - 1;
+                        top_insert(w, tsz, top_limit_all, __shfl_sync(kFull, d, j), __shfl_sync(kFull, e, j));
+                    }
+                }
+                const uint32_t nk2 = refine<METRIC>(g, w, tsz, capc, kept_s, kept_d, staged);
+                for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
+                unlock_node(p.locks, close);
+            }
+        }
+
+        // a node above the current top level becomes the entry point once it is connected: index.hpp:2372-2376
+        if (level > max_level && lane == 0) {
+            const unsigned long long mineEs = ((unsigned long long)(uint32_t)level << 32) | slot;
+            unsigned long long cur = __ldcg(p.entry_state);
+            while ((int)(cur >> 32) < level) {
+                const unsigned long long old = atomicCAS(p.entry_state, cur, mineEs);
+                if (old == cur) break;
+                cur = old;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+template <int METRIC> static cudaError_t launch_build_t(const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(k_build<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
+    if (e != cudaSuccess) return e;
+    k_build<METRIC><<<grid, 32, p.sm.bytes, st>>>(g, p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t st) {
+    switch (metric) {
+    case kCos: return launch_build_t<kCos>(g, p, grid, st);
+    case kIp: return launch_build_t<kIp>(g, p, grid, st);
+    default: return launch_build_t<kL2sq>(g, p, grid, st);
+    }
+}
+
+} // namespace gvss

@@ -1,0 +1,285 @@
+// K5/K6 — exact (brute-force) top-k with DuckDB's distance folds, bit for bit, and K7 — top-k list merge.
+// Restates DistanceOp / CosineDistanceOp / NegativeInnerProductOp (duckdb/extension/core_functions/include/
+// core_functions/array_kernels.hpp:11-105) applied by ArrayGenericFold (array_functions.cpp:145-200) under
+// `ORDER BY array_distance(v, q), rowid LIMIT k` and the vss_join / vss_match macros (hnsw_index_macros.cpp:10-78).
+//
+// Every (row, query) distance is a strict left-to-right fp32 sum with separate multiply and add owned by one thread,
+// so values — and therefore the order, including ties — equal DuckDB's on x86-64. This is the FFMA-class variant the
+// north star allows ("otherwise they use FFMA"); it is FP32-pipe bound, not HBM bound: a 128-row tile of the base is
+// shared through shared memory by QT queries per thread.
+#include "kernels.h"
+
+namespace gvss {
+
+constexpr int kRows = 128;   // base rows per tile = threads per CTA
+constexpr int kDimChunk = 32; // floats per staged chunk
+constexpr int kRowStride = kDimChunk + 4; // 9 x 16 B: conflict-free per-thread float4 reads
+
+__device__ __forceinline__ uint32_t order_key(float d) {
+    if (d != d) return 0xFFFFFFFFu;           // NaN sorts last (DuckDB orders NaN as the greatest value)
+    if (d == 0.0f) return 0x80000000u;        // -0 == +0
+    const uint32_t u = __float_as_uint(d);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+template <char METRIC> __device__ __forceinline__ float fold_finish(float ab, float a2, float b2) {
+    if (METRIC == 'e') return __fsqrt_rn(ab);
+    if (METRIC == 'i') return -ab;
+    const float sim = __fdiv_rn(ab, __fsqrt_rn(__fmul_rn(a2, b2)));
+    const float mn = (1.0f < sim) ? 1.0f : sim;   // std::min(sim, 1)
+    const float mx = (-1.0f < mn) ? mn : -1.0f;   // std::max(-1, .)  (a NaN similarity ends as -1, like DuckDB)
+    return __fsub_rn(1.0f, mx);
+}
+
+// sorted insert of (key, dist) into a k-entry list owned by one warp
+__device__ __forceinline__ void list_insert(unsigned long long *lk, float *ld, uint32_t &size, uint32_t k,
+                                            unsigned long long key, float d) {
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t cnt = 0;
+    for (uint32_t i = lane; i < size; i += 32) cnt += lk[i] < key ? 1u : 0u;
+    const uint32_t pos = __reduce_add_sync(kFull, cnt);
+    if (pos >= k) return;
+    const bool full = size == k;
+    const uint32_t end = full ? size - 1 : size;
+    for (int32_t hi = (int32_t)end; hi > (int32_t)pos; hi -= 32) {
+        const int32_t i = hi - 1 - (int32_t)lane;
+        unsigned long long tk = 0; float td = 0.f;
+        const bool mv = i >= (int32_t)pos;
+        if (mv) { tk = lk[i]; td = ld[i]; }
+        __syncwarp();
+        if (mv) { lk[i + 1] = tk; ld[i + 1] = td; }
+        __syncwarp();
+    }
+    if (lane == 0) { lk[pos] = key; ld[pos] = d; }
+    __syncwarp();
+    if (!full) size++;
+}
+
+// grid.x = query tiles, grid.y = base splits. Output: partial lists [split][nq][k] of (dist, row index).
+template <char METRIC, int QT>
+__global__ void __launch_bounds__(kRows) k_exact(const float *__restrict__ base, uint64_t n, const float *__restrict__ queries,
+                                                uint64_t nq, uint32_t d, uint32_t k, uint64_t rows_per_split,
+                                                unsigned long long *__restrict__ part_key, float *__restrict__ part_dist) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t dpad = (d + 3) / 4 * 4;
+    float *sq = reinterpret_cast<float *>(smem_raw);                 // QT × dpad
+    float *sb = sq + QT * dpad;                                      // 2 × kRows × kRowStride
+    float *sd = sb + 2 * kRows * kRowStride;                         // QT × kRows distances of the current tile
+    unsigned long long *lk = reinterpret_cast<unsigned long long *>(sd + QT * kRows); // QT × k
+    float *ld = reinterpret_cast<float *>(lk + QT * k);              // QT × k
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint64_t q0 = (uint64_t)blockIdx.x * QT;
+    const uint64_t r_begin = (uint64_t)blockIdx.y * rows_per_split;
+    const uint64_t r_end = min(n, r_begin + rows_per_split);
+
+    for (uint32_t i = tid; i < QT * dpad; i += kRows) {
+        const uint32_t j = i / dpad, c = i % dpad;
+        sq[i] = (q0 + j < nq && c < d) ? queries[(q0 + j) * d + c] : 0.0f;
+    }
+    uint32_t lsize[(QT + 3) / 4]; // list sizes of the queries this warp owns (queries warp, warp+4, ...)
+#pragma unroll
+    for (int i = 0; i < (QT + 3) / 4; i++) lsize[i] = 0;
+    __syncthreads();
+
+    const uint32_t nchunk = (dpad + kDimChunk - 1) / kDimChunk;
+    const bool vec4 = (d % 4 == 0);
+    for (uint64_t t0 = r_begin; t0 < r_end; t0 += kRows) {
+        float ab[QT], a2[QT], b2[QT];
+#pragma unroll
+        for (int j = 0; j < QT; j++) { ab[j] = 0.f; a2[j] = 0.f; b2[j] = 0.f; }
+        // stage chunk 0
+        auto load_chunk = [&](uint32_t ch, float4 *regs) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const uint32_t g = tid + kRows * i;      // granule: row = g / 8, 16-byte column = g % 8
+                const uint32_t r = g >> 3, c = (g & 7u) * 4 + ch * kDimChunk;
+                const uint64_t row = t0 + r;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row < r_end && c < d) {
+                    const float *src = base + row * d + c;
+                    if (vec4) v = __ldg(reinterpret_cast<const float4 *>(src));
+                    else { v.x = __ldg(src); if (c + 1 < d) v.y = __ldg(src + 1); if (c + 2 < d) v.z = __ldg(src + 2); if (c + 3 < d) v.w = __ldg(src + 3); }
+                }
+                regs[i] = v;
+            }
+        };
+        auto store_chunk = [&](uint32_t buf, const float4 *regs) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const uint32_t g = tid + kRows * i;
+                const uint32_t r = g >> 3, c4 = g & 7u;
+                *reinterpret_cast<float4 *>(sb + (buf * kRows + r) * kRowStride + c4 * 4) = regs[i];
+            }
+        };
+        float4 regs[8];
+        load_chunk(0, regs);
+        store_chunk(0, regs);
+        __syncthreads();
+        for (uint32_t ch = 0; ch < nchunk; ch++) {
+            const uint32_t buf = ch & 1u;
+            if (ch + 1 < nchunk) load_chunk(ch + 1, regs);
+            const float4 *brow = reinterpret_cast<const float4 *>(sb + (buf * kRows + tid) * kRowStride);
+            const uint32_t nf4 = min((uint32_t)kDimChunk, dpad - ch * kDimChunk) / 4;
+            for (uint32_t c4 = 0; c4 < nf4; c4++) {
+                const float4 x = brow[c4];
+#pragma unroll
+                for (int j = 0; j < QT; j++) {
+                    const float4 y = *reinterpret_cast<const float4 *>(sq + j * dpad + ch * kDimChunk + c4 * 4);
+                    const float xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        if (METRIC == 'e') { const float t = __fsub_rn(xs[e], ys[e]); ab[j] = __fadd_rn(ab[j], __fmul_rn(t, t)); }
+                        else {
+                            ab[j] = __fadd_rn(ab[j], __fmul_rn(xs[e], ys[e]));
+                            if (METRIC == 'c') { a2[j] = __fadd_rn(a2[j], __fmul_rn(xs[e], xs[e])); b2[j] = __fadd_rn(b2[j], __fmul_rn(ys[e], ys[e])); }
+                        }
+                    }
+                }
+            }
+            if (ch + 1 < nchunk) store_chunk(buf ^ 1u, regs);
+            __syncthreads();
+        }
+#pragma unroll
+        for (int j = 0; j < QT; j++) sd[j * kRows + tid] = fold_finish<METRIC>(ab[j], a2[j], b2[j]);
+        __syncthreads();
+        // warp w owns queries w, w+4, ...: filter the tile's 128 distances against the current k-th and insert
+#pragma unroll
+        for (int jj = 0; jj < (QT + 3) / 4; jj++) {
+            const uint32_t j = warp + 4 * jj;
+            if (j >= QT || q0 + j >= nq) continue;
+            unsigned long long *mk = lk + (size_t)j * k;
+            float *md = ld + (size_t)j * k;
+            for (uint32_t rb = 0; rb < kRows; rb += 32) {
+                const uint64_t row = t0 + rb + lane;
+                const float dv = sd[j * kRows + rb + lane];
+                const unsigned long long key = ((unsigned long long)order_key(dv) << 32) | (uint32_t)row;
+                const unsigned long long worst = lsize[jj] == k ? mk[k - 1] : ~0ull;
+                uint32_t m = __ballot_sync(kFull, row < r_end && key < worst);
+                while (m) {
+                    const uint32_t src = __ffs(m) - 1;
+                    m &= m - 1;
+                    const unsigned long long kj = __shfl_sync(kFull, key, src);
+                    const float dj = __shfl_sync(kFull, dv, src);
+                    list_insert(mk, md, lsize[jj], k, kj, dj);
+                }
+            }
+        }
+        __syncthreads();
+    }
+    // write this split's lists
+#pragma unroll
+    for (int jj = 0; jj < (QT + 3) / 4; jj++) {
+        const uint32_t j = warp + 4 * jj;
+        if (j >= QT || q0 + j >= nq) continue;
+        const size_t o = ((size_t)blockIdx.y * nq + (q0 + j)) * k;
+        for (uint32_t i = lane; i < k; i += 32) {
+            const bool have = i < lsize[jj];
+            part_key[o + i] = have ? lk[(size_t)j * k + i] : ~0ull;
+            part_dist[o + i] = have ? ld[(size_t)j * k + i] : CUDART_INF_F;
+        }
+    }
+}
+
+// merge of `shards` ascending lists per query. One warp per query; rank sort over shards×k elements.
+// MODE 0: inputs are (order-key|row, dist) partials of k_exact (unique keys; row -> optional keys[] lookup)
+// MODE 1: inputs are (key i64, dist) lists from different GPUs; order (dist, key), padding entries (key -1) last
+template <int MODE>
+__global__ void k_merge(const unsigned long long *__restrict__ in_key, const float *__restrict__ in_dist, uint32_t shards,
+                        uint64_t nq, uint32_t k, const int64_t *__restrict__ id_map, int64_t *__restrict__ keys_out,
+                        float *__restrict__ dist_out) {
+    const uint64_t q = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t total = shards * k;
+    auto get = [&](uint32_t e, unsigned long long &hi, unsigned long long &lo, float &dv) {
+        const uint32_t s = e / k, i = e % k;
+        const size_t o = ((size_t)s * nq + q) * k + i;
+        dv = in_dist[o];
+        if (MODE == 0) { hi = in_key[o]; lo = e; }
+        else {
+            const long long key = (long long)in_key[o];
+            const bool pad = key < 0 && !(dv < CUDART_INF_F);
+            hi = ((unsigned long long)(pad ? 0xFFFFFFFFu : order_key(dv)) << 32) | (pad ? 0xFFFFFFFFu : 0u);
+            lo = (unsigned long long)key ^ 0x8000000000000000ull; // signed order
+            hi |= 0; // (dist, key) lexicographic; equal pairs cannot occur for disjoint shards
+        }
+    };
+    for (uint32_t e = lane; e < total; e += 32) {
+        unsigned long long hi, lo; float dv;
+        get(e, hi, lo, dv);
+        uint32_t rank = 0;
+        for (uint32_t o = 0; o < total; o++) {
+            unsigned long long h2, l2; float d2;
+            get(o, h2, l2, d2);
+            rank += (h2 < hi || (h2 == hi && (l2 < lo || (l2 == lo && o < e)))) ? 1u : 0u;
+        }
+        if (rank < k) {
+            int64_t id;
+            if (MODE == 0) {
+                const unsigned long long kk = in_key[((size_t)(e / k) * nq + q) * k + (e % k)];
+                if (kk == ~0ull) id = -1;
+                else { const uint32_t row = (uint32_t)(kk & 0xFFFFFFFFull); id = id_map ? id_map[row] : (int64_t)row; }
+            } else id = (int64_t)in_key[((size_t)(e / k) * nq + q) * k + (e % k)];
+            keys_out[q * k + rank] = id;
+            if (dist_out) dist_out[q * k + rank] = dv;
+        }
+    }
+}
+
+template <char METRIC, int QT>
+static cudaError_t run_exact(const float *base, uint64_t n, const int64_t *keys, const float *queries, uint64_t nq, uint32_t d,
+                             uint32_t k, int64_t *ids_out, float *dist_out, cudaStream_t st) {
+    const uint32_t dpad = (d + 3) / 4 * 4;
+    const size_t smem = (size_t)QT * dpad * 4 + 2ull * kRows * kRowStride * 4 + (size_t)QT * kRows * 4 + (size_t)QT * k * 12 + 16;
+    if (smem > 220 * 1024) return cudaErrorInvalidValue;
+    cudaError_t e = cudaFuncSetAttribute(k_exact<METRIC, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const uint64_t qtiles = (nq + QT - 1) / QT;
+    uint64_t splits = 1;
+    if (qtiles < 2ull * sms) splits = (2ull * sms + qtiles - 1) / qtiles;
+    const uint64_t tiles = (n + kRows - 1) / kRows;
+    if (splits > tiles) splits = tiles ? tiles : 1;
+    if (splits > 1024) splits = 1024;
+    const uint64_t rows_per_split = ((tiles + splits - 1) / splits) * kRows;
+    splits = n ? (n + rows_per_split - 1) / rows_per_split : 1;
+    unsigned long long *pk = nullptr; float *pd = nullptr;
+    e = cudaMallocAsync(&pk, splits * nq * k * 8, st);
+    if (e != cudaSuccess) return e;
+    e = cudaMallocAsync(&pd, splits * nq * k * 4, st);
+    if (e != cudaSuccess) { cudaFreeAsync(pk, st); return e; }
+    dim3 grid((unsigned)qtiles, (unsigned)splits);
+    k_exact<METRIC, QT><<<grid, kRows, smem, st>>>(base, n, queries, nq, d, k, rows_per_split, pk, pd);
+    count_launch();
+    const uint32_t wpb = 4;
+    k_merge<0><<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(pk, pd, (uint32_t)splits, nq, k, keys, ids_out, dist_out);
+    count_launch();
+    e = cudaGetLastError();
+    cudaFreeAsync(pk, st);
+    cudaFreeAsync(pd, st);
+    return e;
+}
+
+cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries, uint64_t nq,
+                              uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out, cudaStream_t st) {
+    if (!nq) return cudaSuccess;
+    switch (metric) {
+    case 'c': return run_exact<'c', 8>(base, n, keys, queries, nq, d, k, ids_out, dist_out, st);
+    case 'i': return run_exact<'i', 16>(base, n, keys, queries, nq, d, k, ids_out, dist_out, st);
+    default: return run_exact<'e', 16>(base, n, keys, queries, nq, d, k, ids_out, dist_out, st);
+    }
+}
+
+cudaError_t launch_merge_topk(const int64_t *gk, const float *gd, uint32_t shards, uint64_t nq, uint32_t k, int64_t *keys_out,
+                              float *dist_out, cudaStream_t st) {
+    if (!nq) return cudaSuccess;
+    const uint32_t wpb = 4;
+    k_merge<1><<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(reinterpret_cast<const unsigned long long *>(gk), gd, shards, nq,
+                                                                      k, nullptr, keys_out, dist_out);
+    count_launch();
+    return cudaGetLastError();
+}
+
+} // namespace gvss

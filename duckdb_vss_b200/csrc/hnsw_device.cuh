@@ -1,0 +1,450 @@
+// Warp-level device primitives of the HNSW hot path (sm_100a). One warp owns one query / one insert.
+//
+// Numerics contract: every distance is a strict left-to-right fp32 sum with separate multiply and add
+// (__fmul_rn/__fadd_rn, never contracted into FMA) computed by ONE lane over a whole row, so its bits equal
+// the reference's scalar loops on x86-64 (usearch index_plugins.hpp:981-993 ip, :1006-1026 cos, :1037-1052 l2sq).
+// Rows are brought from HBM into shared memory by TMA bulk copies (cp.async.bulk, 16-byte granules, mbarrier
+// completion) — or, when compiled with GVSS_USE_TMA=0, by coalesced 16-byte cp.async — into a padded layout
+// that makes the per-lane float4 reads bank-conflict free; 32 neighbours are evaluated at once, lane i <-> row i.
+//
+// Control flow contract: the candidate queue (`next`), the result list (`top`) and the acceptance test replay
+// usearch's containers operation by operation (index.hpp:516-645 max_heap_gt, :655-766 sorted_buffer_gt,
+// :3504-3573 search_to_find_in_base_, :3430-3496 search_to_insert_), so results, their order among ties and the
+// traversal counters are identical to the reference on the same graph.
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+#ifndef GVSS_USE_TMA
+#define GVSS_USE_TMA 1
+#endif
+
+namespace gvss {
+
+constexpr uint32_t kInvalid = 0xFFFFFFFFu; // adjacency sentinel / empty visited slot
+constexpr uint32_t kFull = 0xFFFFFFFFu;
+constexpr int kChunk = 128;                // floats of a row staged per step (512 B)
+
+enum Metric : int { kL2sq = 0, kCos = 1, kIp = 2 };
+
+// Device view of the index. Adjacency rows are sentinel-terminated (kInvalid), so a level-0 list of M0=32
+// neighbours is exactly one 128-byte line and needs no separate count.
+struct GraphView {
+    const float *vectors;      // [capacity][dpad] fp32, rows padded with zeros to a multiple of 4 floats (16 B)
+    const int64_t *keys;       // [capacity]
+    uint32_t *nbr0;            // [capacity][stride0]
+    uint32_t *upper;           // [upper blocks][strideU]
+    const uint32_t *upper_off; // [capacity] first upper block of the node (levels 1..L are consecutive blocks)
+    uint32_t dpad, dims, M, M0, stride0, strideU;
+    uint32_t count;
+    uint32_t has_deleted;      // any key == FREE_KEY present (skips the predicate load otherwise)
+};
+
+struct Cand {
+    float d;
+    uint32_t s;
+};
+
+// Per-warp workspace: shared-memory carve-out + global scratch (visited table, queue overflow).
+struct WarpWs {
+    float *q;            // dpad floats: the query / the vector being inserted
+    float *c;            // 2 × kChunk floats: streamed "left-hand" row chunk for node-to-node distances
+    float *stage[2];     // 2 × 32 rows × rstride floats (second buffer only when dpad > kChunk)
+    uint32_t rstride;    // floats between staged rows (odd multiple of 4 floats -> conflict-free LDS.128)
+    float *top_d;        // result list, ascending
+    uint32_t *top_s;
+    Cand *heap;          // candidate queue: first heap_smem entries in shared memory ...
+    Cand *heap_ovf;      // ... the rest in global scratch
+    uint32_t heap_smem, heap_total;
+    uint32_t *vis;       // visited table (open addressing) in global scratch
+    uint32_t vis_mask, vis_limit;
+    uint64_t *mbar;      // 2 mbarriers (one per stage buffer)
+    uint32_t phase[2];
+};
+
+struct Counters {
+    uint32_t computed, cycles, base;
+    uint32_t flags;
+};
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---------------------------------------------------------------------------------------------------------
+// async row staging
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_row(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// distances
+// ---------------------------------------------------------------------------------------------------------
+struct Acc {
+    float ab, a2, b2;
+};
+
+template <int METRIC> __device__ __forceinline__ void acc_step(Acc &r, float a, float b) {
+    if (METRIC == kL2sq) {
+        float t = __fsub_rn(a, b);
+        r.ab = __fadd_rn(r.ab, __fmul_rn(t, t));
+    } else if (METRIC == kIp) {
+        r.ab = __fadd_rn(r.ab, __fmul_rn(a, b));
+    } else {
+        r.ab = __fadd_rn(r.ab, __fmul_rn(a, b));
+        r.a2 = __fadd_rn(r.a2, __fmul_rn(a, a));
+        r.b2 = __fadd_rn(r.b2, __fmul_rn(b, b));
+    }
+}
+template <int METRIC> __device__ __forceinline__ void acc_chunk(Acc &r, const float4 *a, const float4 *b, int n4) {
+#pragma unroll 4
+    for (int i = 0; i < n4; i++) {
+        float4 x = a[i], y = b[i];
+        acc_step<METRIC>(r, x.x, y.x);
+        acc_step<METRIC>(r, x.y, y.y);
+        acc_step<METRIC>(r, x.z, y.z);
+        acc_step<METRIC>(r, x.w, y.w);
+    }
+}
+template <int METRIC> __device__ __forceinline__ float acc_finish(const Acc &r) {
+    if (METRIC == kL2sq) return r.ab;
+    if (METRIC == kIp) return __fsub_rn(1.0f, r.ab);
+    // metric_cos_gt: result_if_zero[a2 == 0][b2 == 0]
+    if (r.a2 == 0.0f && r.b2 == 0.0f) return 0.0f;
+    if (r.a2 == 0.0f || r.b2 == 0.0f) return 1.0f;
+    return __fsub_rn(1.0f, __fdiv_rn(r.ab, __fmul_rn(__fsqrt_rn(r.a2), __fsqrt_rn(r.b2))));
+}
+
+// Where the left-hand vector of a distance batch comes from.
+struct LeftSrc {
+    const float *smem; // whole row resident in shared memory (the query), or nullptr
+    uint32_t slot;     // else: row `slot` of the index, streamed chunk by chunk next to the right-hand rows
+};
+
+// Distances from one left-hand vector to up to 32 rows: lane i (if `active`) gets d(left, vectors[my_slot]).
+// `staged` remembers which row sits in stage[0][lane] so that back-to-back calls over the same rows
+// (neighbour-selection steps) do not touch HBM/L2 again when a row is a single chunk.
+template <int METRIC>
+__device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, LeftSrc left, uint32_t my_slot,
+                                                bool active, uint32_t &staged) {
+    const uint32_t lane = lane_id();
+    const uint32_t nchunks = (g.dpad + kChunk - 1) / kChunk;
+    const bool single = nchunks == 1;
+    const bool stream_left = left.smem == nullptr;
+    Acc acc = {0.0f, 0.0f, 0.0f};
+
+    auto issue = [&](uint32_t ch) {
+        const uint32_t buf = ch & 1u;
+        const uint32_t off = ch * kChunk;
+        const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
+        const bool need = active && !(single && staged == my_slot);
+        const uint32_t need_mask = __ballot_sync(kFull, need);
+        const uint32_t ncopy = __popc(need_mask) + (stream_left ? 1u : 0u);
+        if (ncopy == 0) return false;
+#if GVSS_USE_TMA
+        if (lane == 0) mbar_expect_tx(&w.mbar[buf], ncopy * nfl * 4u);
+        __syncwarp();
+        if (need) tma_row(w.stage[buf] + lane * w.rstride, g.vectors + (size_t)my_slot * g.dpad + off, nfl * 4u, &w.mbar[buf]);
+        if (stream_left && lane == 0)
+            tma_row(w.c + buf * kChunk, g.vectors + (size_t)left.slot * g.dpad + off, nfl * 4u, &w.mbar[buf]);
+#else
+        for (uint32_t m = need_mask; m; m &= m - 1) {
+            const uint32_t src = __ffs(m) - 1;
+            const uint32_t s = __shfl_sync(kFull, my_slot, src);
+            if (lane * 4 < nfl) cp_async16(w.stage[buf] + src * w.rstride + lane * 4, g.vectors + (size_t)s * g.dpad + off + lane * 4);
+        }
+        if (stream_left && lane * 4 < nfl)
+            cp_async16(w.c + buf * kChunk + lane * 4, g.vectors + (size_t)left.slot * g.dpad + off + lane * 4);
+        cp_async_commit();
+#endif
+        return true;
+    };
+
+    bool pending = issue(0);
+    for (uint32_t ch = 0; ch < nchunks; ch++) {
+        const uint32_t buf = ch & 1u;
+        bool pending_next = false;
+        if (ch + 1 < nchunks) pending_next = issue(ch + 1);
+        if (pending) {
+#if GVSS_USE_TMA
+            mbar_wait(&w.mbar[buf], w.phase[buf]);
+            w.phase[buf] ^= 1u;
+#else
+            if (pending_next) cp_async_wait<1>(); else cp_async_wait<0>();
+            __syncwarp();
+#endif
+        }
+        const uint32_t off = ch * kChunk;
+        const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
+        if (active) {
+            const float4 *a = reinterpret_cast<const float4 *>(stream_left ? (w.c + buf * kChunk) : (left.smem + off));
+            const float4 *b = reinterpret_cast<const float4 *>(w.stage[buf] + lane * w.rstride);
+            acc_chunk<METRIC>(acc, a, b, (int)(nfl / 4));
+        }
+        __syncwarp(); // all lanes are done reading this buffer before it is refilled
+        pending = pending_next;
+    }
+    if (active) staged = single ? my_slot : kInvalid;
+    return acc_finish<METRIC>(acc);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// visited set: open addressing in global scratch, one table per warp (any exact set is equivalent to
+// usearch's growing_hash_set_gt, index.hpp:852-970 — only membership matters)
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void vis_clear(WarpWs &w) {
+    uint4 *p = reinterpret_cast<uint4 *>(w.vis);
+    const uint32_t n4 = (w.vis_mask + 1) / 4;
+    const uint4 e = make_uint4(kInvalid, kInvalid, kInvalid, kInvalid);
+    for (uint32_t i = lane_id(); i < n4; i += 32) p[i] = e;
+    __syncwarp();
+}
+// returns true when `key` was not yet present (and is now)
+__device__ __forceinline__ bool vis_insert(WarpWs &w, uint32_t key) {
+    uint32_t h = (key * 2654435761u) >> 7;
+    for (;;) {
+        h &= w.vis_mask;
+        const uint32_t old = atomicCAS(&w.vis[h], kInvalid, key);
+        if (old == kInvalid) return true;
+        if (old == key) return false;
+        h++;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// candidate queue: binary heap with usearch's shift_up / shift_down (index.hpp:624-644). The reference keeps
+// {-distance, slot} in a max-heap; here +distance in a min-heap with every comparison mirrored. All lanes run
+// the same scalar code on broadcast shared-memory reads, so no shuffles or barriers are needed.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ Cand heap_get(const WarpWs &w, uint32_t i) {
+    return i < w.heap_smem ? w.heap[i] : w.heap_ovf[i - w.heap_smem];
+}
+__device__ __forceinline__ void heap_set(WarpWs &w, uint32_t i, Cand v) {
+    if (i < w.heap_smem) w.heap[i] = v; else w.heap_ovf[i - w.heap_smem] = v;
+}
+__device__ __forceinline__ bool heap_push(WarpWs &w, uint32_t &size, float d, uint32_t s) {
+    if (size >= w.heap_total) return false;
+    uint32_t i = size++;
+    while (i) {
+        const uint32_t p = (i - 1) >> 1;
+        const Cand pe = heap_get(w, p);
+        if (!(pe.d > d)) break; // less(parent, child) on negated distances
+        heap_set(w, i, pe);
+        i = p;
+    }
+    heap_set(w, i, Cand{d, s});
+    return true;
+}
+__device__ __forceinline__ void heap_pop(WarpWs &w, uint32_t &size) {
+    size--;
+    if (size == 0) return;
+    const Cand x = heap_get(w, size);
+    uint32_t i = 0;
+    for (;;) {
+        uint32_t mx = i;
+        float best = x.d;
+        const uint32_t l = 2 * i + 1, r = 2 * i + 2;
+        Cand le, re;
+        if (l < size) { le = heap_get(w, l); if (best > le.d) { mx = l; best = le.d; } }
+        if (r < size) { re = heap_get(w, r); if (best > re.d) { mx = r; } }
+        if (mx == i) break;
+        heap_set(w, i, mx == l ? le : re);
+        i = mx;
+    }
+    heap_set(w, i, x);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// result list: sorted_buffer_gt (index.hpp:725-749). lower_bound => an element equal to existing ones goes
+// BEFORE them; at the limit the worst element is dropped; position == limit rejects.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool top_insert(WarpWs &w, uint32_t &size, uint32_t limit, float d, uint32_t s) {
+    const uint32_t lane = lane_id();
+    uint32_t cnt = 0;
+    for (uint32_t i = lane; i < size; i += 32) cnt += (w.top_d[i] < d) ? 1u : 0u;
+    const uint32_t pos = __reduce_add_sync(kFull, cnt);
+    if (pos == limit) return false;
+    const bool full = size == limit;
+    const uint32_t end = full ? size - 1 : size; // elements [pos, end) move up by one
+    // move in 32-wide windows from the top so that no element is overwritten before it is read
+    for (int32_t hi = (int32_t)end; hi > (int32_t)pos; hi -= 32) {
+        const int32_t i = hi - 1 - (int32_t)lane;
+        float td = 0.f;
+        uint32_t ts = 0;
+        const bool mv = i >= (int32_t)pos;
+        if (mv) { td = w.top_d[i]; ts = w.top_s[i]; }
+        __syncwarp();
+        if (mv) { w.top_d[i + 1] = td; w.top_s[i + 1] = ts; }
+        __syncwarp();
+    }
+    if (lane == 0) { w.top_d[pos] = d; w.top_s[pos] = s; }
+    __syncwarp();
+    if (!full) size++;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// adjacency access
+// ---------------------------------------------------------------------------------------------------------
+template <bool VOLATILE> __device__ __forceinline__ uint32_t ld_adj(const uint32_t *p) {
+    return VOLATILE ? __ldcg(p) : __ldg(p);
+}
+__device__ __forceinline__ uint32_t *list_ptr(const GraphView &g, uint32_t slot, int level, uint32_t &cap) {
+    if (level == 0) { cap = g.M0; return g.nbr0 + (size_t)slot * g.stride0; }
+    cap = g.M;
+    return g.upper + ((size_t)__ldg(&g.upper_off[slot]) + (uint32_t)(level - 1)) * g.strideU;
+}
+
+// search_for_one_ (index.hpp:3384-3422): greedy descent from `closest` through levels begin..end+1.
+template <int METRIC, bool VOLATILE>
+__device__ __forceinline__ uint32_t greedy_descent(const GraphView &g, WarpWs &w, uint32_t closest, int begin_level,
+                                                   int end_level, Counters &cnt, uint32_t &staged) {
+    const uint32_t lane = lane_id();
+    LeftSrc q{w.q, 0};
+    float cd = warp_distances<METRIC>(g, w, q, closest, lane == 0, staged);
+    cd = __shfl_sync(kFull, cd, 0);
+    cnt.computed++;
+    for (int level = begin_level; level > end_level; --level) {
+        bool changed;
+        do {
+            changed = false;
+            uint32_t cap;
+            const uint32_t *list = list_ptr(g, closest, level, cap);
+            for (uint32_t base = 0; base < cap; base += 32) {
+                const uint32_t idx = base + lane;
+                const uint32_t s = idx < cap ? ld_adj<VOLATILE>(list + idx) : kInvalid;
+                const bool valid = s != kInvalid;
+                const uint32_t vmask = __ballot_sync(kFull, valid);
+                if (!vmask) break;
+                cnt.computed += __popc(vmask);
+                const float d = warp_distances<METRIC>(g, w, q, s, valid, staged);
+                // sequential scan with a running minimum == first strict minimum in list order
+                float best = valid ? d : CUDART_INF_F;
+                uint32_t bl = lane;
+                bool ok = valid && (d < cd);
+                uint32_t okmask = __ballot_sync(kFull, ok);
+                if (okmask) {
+                    // among lanes that beat cd, the strict running minimum picks the smallest value, earliest lane on ties
+                    if (!ok) best = CUDART_INF_F;
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) {
+                        const float ob = __shfl_xor_sync(kFull, best, o);
+                        const uint32_t ol = __shfl_xor_sync(kFull, bl, o);
+                        if (ob < best || (ob == best && ol < bl)) { best = ob; bl = ol; }
+                    }
+                    cd = best;
+                    closest = __shfl_sync(kFull, s, bl);
+                    changed = true;
+                }
+            }
+            cnt.cycles++;
+        } while (changed);
+    }
+    return closest;
+}
+
+// search_to_find_in_base_ (INSERT=false, index.hpp:3504-3573) / search_to_insert_ (INSERT=true, :3430-3496).
+// On return `top` (w.top_d/top_s, ascending) holds `top_size` results.
+template <int METRIC, bool INSERT, bool VOLATILE>
+__device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, uint32_t limit, int level,
+                                            uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged) {
+    const uint32_t lane = lane_id();
+    LeftSrc q{w.q, 0};
+    uint32_t heap_size = 0, nvis = 1;
+    top_size = 0;
+    vis_clear(w);
+
+    float radius = warp_distances<METRIC>(g, w, q, start, lane == 0, staged);
+    radius = __shfl_sync(kFull, radius, 0);
+    cnt.computed++;
+    heap_push(w, heap_size, radius, start);
+    if (lane == 0) vis_insert(w, start);
+    const bool start_ok = INSERT || !g.has_deleted || __ldg(&g.keys[start]) != INT64_MAX;
+    if (start_ok) {
+        if (lane == 0) { w.top_d[0] = radius; w.top_s[0] = start; }
+        top_size = 1;
+    } else {
+        radius = CUDART_INF_F; // reference reads top.top() of an empty buffer here (UB); +inf is the documented choice
+    }
+    __syncwarp();
+
+    while (heap_size) {
+        const Cand c = heap_get(w, 0);
+        if (INSERT) { if (c.d > radius && top_size == limit) break; }
+        else if (c.d > radius) break;
+        heap_pop(w, heap_size);
+        cnt.cycles++;
+        cnt.base++;
+        if (INSERT && c.s == new_slot) continue;
+
+        uint32_t cap;
+        const uint32_t *list = list_ptr(g, c.s, level, cap);
+        for (uint32_t base = 0; base < cap; base += 32) {
+            const uint32_t idx = base + lane;
+            const uint32_t s = idx < cap ? ld_adj<VOLATILE>(list + idx) : kInvalid;
+            const bool valid = s != kInvalid && s < g.count;
+            if (!__ballot_sync(kFull, s != kInvalid)) break;
+            // visits.set(): first occurrence wins; duplicates inside one list resolve to the earliest lane
+            const uint32_t same = __match_any_sync(kFull, s);
+            const bool leader = valid && (uint32_t)(__ffs(same) - 1) == lane;
+            bool isnew = false;
+            if (leader && nvis < w.vis_limit) isnew = vis_insert(w, s);
+            const uint32_t nmask = __ballot_sync(kFull, isnew);
+            if (nvis >= w.vis_limit && __ballot_sync(kFull, leader)) cnt.flags |= 1u;
+            if (!nmask) continue;
+            nvis += __popc(nmask);
+            cnt.computed += __popc(nmask);
+            const float d = warp_distances<METRIC>(g, w, q, s, isnew, staged);
+
+            // replay the acceptance test in list order; candidates that cannot pass once `top` is full are skipped
+            const bool pre = isnew && (top_size < limit || d < radius);
+            uint32_t cmask = __ballot_sync(kFull, pre);
+            while (cmask) {
+                const uint32_t src = __ffs(cmask) - 1;
+                cmask &= cmask - 1;
+                const float dj = __shfl_sync(kFull, d, src);
+                const uint32_t sj = __shfl_sync(kFull, s, src);
+                if (top_size < limit || dj < radius) {
+                    if (!heap_push(w, heap_size, dj, sj)) cnt.flags |= 1u;
+                    const bool ok = INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX;
+                    if (ok) top_insert(w, top_size, limit, dj, sj);
+                    radius = top_size ? w.top_d[top_size - 1] : CUDART_INF_F;
+                }
+            }
+        }
+    }
+}
+
+} // namespace gvss

@@ -1,0 +1,66 @@
+// Host-visible launch interface of the CUDA kernels (internal to libgvss; the public boundary is include/gvss.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/gvss.h"
+#include "hnsw_device.cuh"
+
+namespace gvss {
+
+// shared-memory carve-out of one warp (one CTA = one warp, so a CTA never needs __syncthreads)
+struct SmemLayout {
+    uint32_t off_mbar, off_stage0, off_stage1, off_c, off_q, off_heap, off_top_d, off_top_s, off_misc;
+    uint32_t rstride, heap_smem, top_cap, bytes;
+};
+SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes);
+
+// global scratch of one warp: visited table (vis_slots u32) followed by the queue overflow (heap_ovf Cand)
+struct ScratchLayout {
+    uint32_t vis_slots, vis_limit, heap_ovf;
+    size_t bytes_per_warp;
+};
+ScratchLayout make_scratch_layout(uint32_t beam);
+
+struct SearchParams {
+    const float *queries;
+    uint64_t nq;
+    uint32_t k, limit;
+    int64_t *keys_out;
+    float *dist_out;
+    uint32_t *counts_out;
+    gvss_search_stats *stats_out;
+    uint32_t entry;
+    int32_t max_level;
+    unsigned long long *work_counter;
+    uint8_t *scratch;
+    ScratchLayout sl;
+    SmemLayout sm;
+};
+// grid = number of resident warps; returns cudaError
+cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);
+// how many single-warp CTAs of the search / build kernel fit the device at this shared-memory size
+uint32_t resident_warps(int device, uint32_t smem_bytes, bool build);
+
+struct BuildParams {
+    const uint32_t *slots;   // nodes to insert, in order
+    uint32_t begin, end;     // this launch inserts slots[begin..end)
+    const int16_t *levels;   // [capacity]
+    unsigned long long *entry_state; // (max_level << 32) | entry_slot ; ~0ull while the graph is empty
+    unsigned long long *work_counter;
+    uint32_t *locks;         // [capacity] per-node spin locks (index.hpp:3214-3224 nodes_mutexes_)
+    uint32_t ef_add;
+    uint8_t *scratch;
+    ScratchLayout sl;
+    SmemLayout sm;
+};
+cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t stream);
+
+cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries,
+                              uint64_t nq, uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out,
+                              cudaStream_t stream);
+cudaError_t launch_merge_topk(const int64_t *gk, const float *gd, uint32_t shards, uint64_t nq, uint32_t k,
+                              int64_t *keys_out, float *dist_out, cudaStream_t stream);
+
+void count_launch(uint64_t n = 1);
+
+} // namespace gvss

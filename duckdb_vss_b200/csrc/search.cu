@@ -1,0 +1,138 @@
+// K1 — batched HNSW search: one warp per query, persistent warps pulling queries from a work counter.
+// Replaces index_gt::search (usearch index.hpp:2480-2534) = search_for_one_ (:3384-3422) + search_to_find_in_base_
+// (:3504-3573) as called by index_dense_gt::search_ (index_dense.hpp:1797-1827) from HNSWIndex::InitializeScan /
+// ExecuteMultiScan (hnsw_index.cpp:285-311, 353-367).
+#include "kernels.h"
+
+namespace gvss {
+
+__device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
+                                      const ScratchLayout &sl) {
+    w.mbar = reinterpret_cast<uint64_t *>(smem + sm.off_mbar);
+    w.stage[0] = reinterpret_cast<float *>(smem + sm.off_stage0);
+    w.stage[1] = reinterpret_cast<float *>(smem + sm.off_stage1);
+    w.c = reinterpret_cast<float *>(smem + sm.off_c);
+    w.q = reinterpret_cast<float *>(smem + sm.off_q);
+    w.heap = reinterpret_cast<Cand *>(smem + sm.off_heap);
+    w.top_d = reinterpret_cast<float *>(smem + sm.off_top_d);
+    w.top_s = reinterpret_cast<uint32_t *>(smem + sm.off_top_s);
+    w.rstride = sm.rstride;
+    w.heap_smem = sm.heap_smem;
+    uint8_t *base = scratch + (size_t)blockIdx.x * sl.bytes_per_warp;
+    w.vis = reinterpret_cast<uint32_t *>(base);
+    w.vis_mask = sl.vis_slots - 1;
+    w.vis_limit = sl.vis_limit;
+    w.heap_ovf = reinterpret_cast<Cand *>(base + (size_t)sl.vis_slots * 4);
+    w.heap_total = sm.heap_smem + sl.heap_ovf;
+    w.phase[0] = w.phase[1] = 0;
+    if (lane_id() == 0) {
+        mbar_init(&w.mbar[0], 1);
+        mbar_init(&w.mbar[1], 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+}
+
+template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g, SearchParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    WarpWs w;
+    carve(w, smem, p.sm, p.scratch, p.sl);
+    const uint32_t lane = lane_id();
+    uint32_t staged = kInvalid;
+
+    for (;;) {
+        unsigned long long qi = 0;
+        if (lane == 0) qi = atomicAdd(p.work_counter, 1ull);
+        qi = __shfl_sync(kFull, qi, 0);
+        if (qi >= p.nq) break;
+
+        const float *qsrc = p.queries + qi * g.dims;
+        for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = i < g.dims ? __ldg(qsrc + i) : 0.0f;
+        __syncwarp();
+
+        Counters cnt = {0, 0, 0, 0};
+        uint32_t top_size = 0;
+        if (g.count && p.k) {
+            const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
+        }
+        const uint32_t n = min(top_size, p.k); // top.shrink(wanted), index.hpp:2526-2527
+        for (uint32_t i = lane; i < p.k; i += 32) {
+            const bool have = i < n;
+            p.keys_out[qi * p.k + i] = have ? __ldg(&g.keys[w.top_s[i]]) : -1; // dump_to: slot -> key, index.hpp:2252-2258
+            if (p.dist_out) p.dist_out[qi * p.k + i] = have ? w.top_d[i] : CUDART_INF_F;
+        }
+        if (lane == 0) {
+            if (p.counts_out) p.counts_out[qi] = n;
+            if (p.stats_out) p.stats_out[qi] = gvss_search_stats{cnt.computed, cnt.cycles, cnt.base, cnt.flags};
+        }
+        __syncwarp();
+    }
+}
+
+SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes) {
+    SmemLayout s{};
+    const uint32_t chunkf = dpad < (uint32_t)kChunk ? dpad : (uint32_t)kChunk;
+    s.rstride = chunkf + (((chunkf / 4) % 2 == 0) ? 4u : 0u); // odd number of 16-byte granules per row
+    const uint32_t stage_bytes = 32u * s.rstride * 4u;
+    const bool two = dpad > (uint32_t)kChunk;
+    uint32_t off = 0;
+    auto take = [&](uint32_t bytes, uint32_t align) { off = (off + align - 1) / align * align; uint32_t o = off; off += bytes; return o; };
+    s.off_mbar = take(16, 16);
+    s.off_stage0 = take(stage_bytes, 128);
+    s.off_stage1 = two ? take(stage_bytes, 128) : s.off_stage0;
+    s.off_c = take(2 * kChunk * 4, 128);
+    s.off_q = take(dpad * 4, 16);
+    s.heap_smem = heap_smem;
+    s.off_heap = take(heap_smem * 8, 16);
+    s.top_cap = top_cap;
+    s.off_top_d = take(top_cap * 4, 16);
+    s.off_top_s = take(top_cap * 4, 16);
+    s.off_misc = take(misc_bytes, 16);
+    s.bytes = (off + 127) / 128 * 128;
+    return s;
+}
+
+ScratchLayout make_scratch_layout(uint32_t beam) {
+    // visited members per search ~ 20*beam + 500 on the measured data sets; 64*beam slots
+    // (min 4096) keep the table under ~40 % load, the kernel flags a query that would exceed 75 %.
+    ScratchLayout s{};
+    uint32_t want = beam * 64u;
+    if (want < 4096u) want = 4096u;
+    uint32_t v = 4096u;
+    while (v < want) v <<= 1;
+    s.vis_slots = v;
+    s.vis_limit = v / 4 * 3 - 32;
+    s.heap_ovf = v; // every queue entry was a newly visited node, so the queue can never outgrow the table
+    s.bytes_per_warp = (size_t)v * 4 + (size_t)s.heap_ovf * 8;
+    return s;
+}
+
+uint32_t resident_warps(int device, uint32_t smem_bytes, bool build) {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0;
+    size_t per_sm = prop.sharedMemPerMultiprocessor;
+    uint32_t by_smem = (uint32_t)(per_sm / (smem_bytes + 1024)); // 1 KB is reserved per CTA
+    uint32_t cap = build ? 16u : 32u; // build warps hold more registers/scratch; 32 = CTA-per-SM limit
+    if (by_smem > cap) by_smem = cap;
+    if (by_smem < 1) by_smem = 1;
+    return by_smem * (uint32_t)prop.multiProcessorCount;
+}
+
+template <int METRIC> static cudaError_t launch_search_t(const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(k_search<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
+    if (e != cudaSuccess) return e;
+    k_search<METRIC><<<grid, 32, p.sm.bytes, st>>>(g, p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
+    switch (metric) {
+    case kCos: return launch_search_t<kCos>(g, p, grid, st);
+    case kIp: return launch_search_t<kIp>(g, p, grid, st);
+    default: return launch_search_t<kL2sq>(g, p, grid, st);
+    }
+}
+
+} // namespace gvss

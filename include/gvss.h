@@ -1,0 +1,159 @@
+/* gvss — C ABI of the B200-native HNSW hot path that replaces usearch's index_dense_gt<row_t>
+ * inside DuckDB's vss extension (reference: duckdb/duckdb_vss).
+ *
+ * The drop-in boundary is the value member `HNSWIndex::index`
+ * (reference src/include/hnsw/hnsw_index.hpp:28,39). Every entry point below cites the reference
+ * call site / usearch method it stands in for. Rules of the ABI:
+ *   - plain C: opaque handle, plain pointers and sizes, no C++/torch types, no exceptions;
+ *   - every function returns 0 on success, non-zero on failure; gvss_last_error() gives the
+ *     message of the calling thread's last failure (static lifetime until that thread's next call);
+ *   - input pointers are borrowed for the duration of the call, outputs are caller-allocated;
+ *   - pointers are HOST memory unless the function name ends in `_device`;
+ *   - there is no CPU fallback: with no CUDA device every compute entry point fails with an error.
+ *
+ * Threading (mirrors how the extension calls usearch): gvss_add may be called from
+ * `host_threads` threads at once with distinct thread ids (PhysicalCreateHNSWIndex,
+ * hnsw_index_physical_create.cpp:144-205); gvss_search* may run concurrently with other searches
+ * (shared side of HNSWIndex::rwlock); everything else is called with the exclusive side held.
+ */
+#ifndef GVSS_H
+#define GVSS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GVSS_METRIC_L2SQ 'e' /* metric_kind_t::l2sq_k, index_plugins.hpp:103-109 (values are part of the file format) */
+#define GVSS_METRIC_COS 'c'  /* metric_kind_t::cos_k */
+#define GVSS_METRIC_IP 'i'   /* metric_kind_t::ip_k  */
+
+#define GVSS_FREE_KEY INT64_MAX /* key written into removed nodes, index_dense.hpp:1246-1250 */
+
+typedef struct gvss_index gvss_index;
+
+/* index_dense_config_t + metric_punned_t as filled by the HNSWIndex ctor (hnsw_index.cpp:140-189).
+ * Zero means "usearch default": M=16, M0=2*M, ef_construction=128, ef_search=64 (index.hpp:1097-1107,1125). */
+typedef struct gvss_config {
+    uint32_t dimensions;
+    char metric;              /* GVSS_METRIC_* */
+    uint32_t connectivity;      /* M  */
+    uint32_t connectivity_base; /* M0 */
+    uint32_t expansion_add;     /* ef_construction */
+    uint32_t expansion_search;  /* ef_search */
+    int32_t device;             /* CUDA ordinal; -1 = current device */
+} gvss_config;
+
+/* index_dense_gt::stats_t per level (index.hpp:2612-2635; hnsw_index_pragmas.cpp:121-135) */
+typedef struct gvss_level_stats {
+    uint64_t nodes, edges, max_edges, allocated_bytes;
+} gvss_level_stats;
+
+typedef struct gvss_info {
+    uint64_t size;         /* present (non-removed) members: index.size(), hnsw_index.cpp:210,463,481 */
+    uint64_t capacity;     /* index.capacity(), hnsw_index.cpp:416,427 */
+    uint64_t node_count;   /* graph nodes incl. removed slots */
+    uint64_t max_level;    /* index.max_level(), hnsw_index.cpp:266 */
+    uint64_t memory_usage; /* index.memory_usage(), hnsw_index.cpp:272,558 */
+    uint64_t dimensions;   /* index.dimensions(), hnsw_index.cpp:216 */
+    uint32_t connectivity, connectivity_base, expansion_add, expansion_search;
+    char metric;           /* index.metric().metric_kind(), hnsw_index.cpp:220 */
+} gvss_info;
+
+/* per-query traversal counters, same meaning as usearch's search_result_t (index.hpp:2187-2192) */
+typedef struct gvss_search_stats {
+    uint32_t computed_distances; /* context_t::computed_distances_count delta */
+    uint32_t visited_members;    /* context_t::iteration_cycles delta = level-0 expansions + upper-level hops */
+    uint32_t base_expansions;    /* level-0 expansions only */
+    uint32_t flags;              /* bit0: visited-table overflow (query was re-run with a larger table) */
+} gvss_search_stats;
+
+/* --- lifetime ----------------------------------------------------------------------------------------------- */
+/* index_dense_gt<row_t>::make(metric, config), hnsw_index.cpp:162-189 */
+int gvss_create(const gvss_config *config, gvss_index **out);
+void gvss_destroy(gvss_index *index);
+/* index.reset(), hnsw_index.cpp:384 */
+int gvss_reset(gvss_index *index);
+/* index.reserve(n) / index.reserve({members, threads}), hnsw_index.cpp:208,429; hnsw_index_physical_create.cpp:296.
+ * Grow only; thread ids 0..host_threads-1 become valid for gvss_add. Not concurrent with gvss_add. */
+int gvss_reserve(gvss_index *index, uint64_t members, uint32_t host_threads);
+
+/* --- construction ------------------------------------------------------------------------------------------- */
+/* index.add(key, vec, thread), hnsw_index_physical_create.cpp:184 and hnsw_index.cpp:443. Copies `vec` before
+ * returning; only stages the row (graph work happens in gvss_flush or the next call that needs a consistent
+ * graph). Fails with "Reserve capacity ahead of insertions!" (index.hpp:2332-2335) when full and with
+ * "Duplicate keys not allowed in high-level wrappers" (index_dense.hpp:1752-1753) is NOT checked, like the
+ * extension's configuration (enable_key_lookups=false makes contains() always false). */
+int gvss_add(gvss_index *index, int64_t key, const float *vec, uint32_t host_thread);
+/* n rows, row-major n×dimensions — the layout HNSWIndex::Construct already has after Flatten (hnsw_index.cpp:399-406) */
+int gvss_add_batch(gvss_index *index, const int64_t *keys, const float *vecs, uint64_t n);
+/* Same with rows already resident on the index's device (bulk-build benchmark path: H2D excluded). */
+int gvss_add_batch_device(gvss_index *index, const int64_t *keys_host, const float *vecs_device, uint64_t n);
+/* Insert everything staged: level draw (index.hpp:3315-3319), per-level beam search (search_to_insert_,
+ * index.hpp:3430-3496), neighbour-selection heuristic (refine_, :3602-3638), reverse links with re-pruning
+ * (reconnect_neighbor_nodes_, :3270-3313) — as sm_100a kernels. */
+int gvss_flush(gvss_index *index);
+/* Upper bound on vectors inserted concurrently by gvss_flush (0 = as many as the GPU holds). The role the thread count
+ * plays in index.reserve({members, threads}) (hnsw_index_physical_create.cpp:296; index_limits_t, index.hpp:1134-1140):
+ * with 1 the build is sequential and reproduces the reference's single-thread graph byte for byte. */
+int gvss_set_build_concurrency(gvss_index *index, uint32_t max_concurrent_inserts);
+/* index.remove(key), hnsw_index.cpp:478: lazy delete (index_dense.hpp:1228-1255); unknown key: *removed = 0. */
+int gvss_remove(gvss_index *index, int64_t key, uint64_t *removed);
+/* index.compact(), hnsw_index.cpp:458 */
+int gvss_compact(gvss_index *index);
+
+/* --- search -------------------------------------------------------------------------------------------------- */
+/* index.ef_search(query, k, ef) for nq queries at once (hnsw_index.cpp:303-309 single query, :359-364 index join).
+ * keys_out: nq×k row ids ascending by distance (unused tail = -1); dist_out (nq×k, may be NULL): the index metric
+ * (l2sq / 1-cos / 1-ip), unused tail = +inf; counts_out (nq, may be NULL): results per query (<= k);
+ * stats_out (nq, may be NULL). ef == 0 means 64 (index.hpp:2493-2494); beam = max(ef, k) (index.hpp:2512). */
+int gvss_search(gvss_index *index, const float *queries, uint64_t nq, uint32_t k, uint32_t ef, int64_t *keys_out,
+                float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out);
+/* Same with every buffer resident on the index's device; runs on `cuda_stream` (a cudaStream_t, 0 = default stream)
+ * and returns without synchronising the stream. queries: nq×dimensions, 16-byte aligned. */
+int gvss_search_device(gvss_index *index, const float *queries, uint64_t nq, uint32_t k, uint32_t ef,
+                       int64_t *keys_out, float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out,
+                       void *cuda_stream);
+
+/* --- persistence: usearch v2.12 stream, byte-compatible in both directions ------------ */
+/* index.save_to_stream(cb), hnsw_index.cpp:526-529 (index_dense.hpp:811-878, index.hpp:2709-2749).
+ * `write` returns non-zero on success (like the usearch callback returning true). */
+int gvss_save(gvss_index *index, int (*write)(void *user, const void *data, size_t size), void *user);
+/* index.load_from_stream(cb), hnsw_index.cpp:204-205 (index_dense.hpp:900-973, index.hpp:2755-2807) */
+int gvss_load(gvss_index *index, int (*read)(void *user, void *data, size_t size), void *user);
+/* index.serialized_length() (index_dense.hpp:883-891) */
+int gvss_serialized_length(gvss_index *index, uint64_t *bytes);
+
+/* --- introspection ------------------------------------------------------------------------------------------- */
+int gvss_get_info(gvss_index *index, gvss_info *out);
+/* index.stats(level), hnsw_index.cpp:271-273 */
+int gvss_get_level_stats(gvss_index *index, uint32_t level, gvss_level_stats *out);
+
+/* --- exact (brute-force) top-k: the comparator behind `ORDER BY array_distance(v, q), rowid LIMIT k`, the vss_join /
+ * vss_match macros (hnsw_index_macros.cpp:10-78) and the ground truth for recall. Distances follow DuckDB's folds
+ * bit for bit (array_kernels.hpp:11-105: 'e' = sqrt(sum (x-y)^2), 'c' = 1 - clamp(xy / sqrt(xx*yy)), 'i' = -sum xy);
+ * ties are broken by the smaller row index. ids_out: nq×k indices into `base` (or keys[idx] when keys != NULL). */
+int gvss_exact_topk(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries,
+                    uint64_t nq, uint32_t dimensions, uint32_t k, int64_t *ids_out, float *dist_out);
+int gvss_exact_topk_device(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries,
+                           uint64_t nq, uint32_t dimensions, uint32_t k, int64_t *ids_out, float *dist_out,
+                           void *cuda_stream);
+
+/* --- multi-GPU: merge of per-shard top-k lists after the all-gather (no reference counterpart:
+ * the reference is single-process). gathered_*: shards×nq×k on the device, each list ascending; output nq×k
+ * ordered by (distance, key). */
+int gvss_merge_topk_device(const int64_t *gathered_keys, const float *gathered_dist, uint32_t shards, uint64_t nq,
+                           uint32_t k, int64_t *keys_out, float *dist_out, void *cuda_stream);
+
+/* --- misc ---------------------------------------------------------------------------------------------------- */
+const char *gvss_last_error(void);
+const char *gvss_version(void);
+/* number of kernels this library has launched in the calling process (bench.py's `gpu_launches`) */
+uint64_t gvss_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GVSS_H */

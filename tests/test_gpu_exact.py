@@ -1,0 +1,71 @@
+"""GPU parity #2: exact brute-force top-k ids and distances are bit-exact against DuckDB's array_distance /
+array_cosine_distance / array_negative_inner_product folds ordered by (distance, rowid); plus the top-k merge."""
+import numpy as np
+import pytest
+import duckdb_vss_b200 as gv
+from duckdb_vss_b200 import synth
+from conftest import golden_cases, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_exact_topk_matches_golden_duckdb_folds(name):
+    z, _ = load_golden(name)
+    ids, dist = gv.exact_topk(str(z["metric"]), z["base"], z["queries"], 10)
+    np.testing.assert_array_equal(ids, z["exact_ids"])
+    np.testing.assert_array_equal(dist.view(np.uint32), z["exact_dist"].view(np.uint32))
+
+
+def test_duckdb_known_answers():
+    f = lambda *v: np.array([v], np.float32)
+    base = np.array([[1, 2, 3], [2, 2, 3], [7, 8, 9], [-1, -2, -3], [0, 0, 0]], np.float32)
+    ids, dist = gv.exact_topk("l2sq", base, f(1, 2, 3), 3)     # array_distance.test:20-27
+    assert list(ids[0]) == [0, 1, 4] and dist[0][0] == 0.0 and dist[0][1] == 1.0
+    ids, dist = gv.exact_topk("cosine", base, f(1, 2, 3), 5)   # array_cosine_distance.test:26-33 (+ zero vector -> 2.0)
+    assert ids[0][0] == 0 and abs(dist[0][0]) < 1e-7 and dist[0][-1] == 2.0 and set(ids[0][-2:]) == {3, 4}
+    ids, dist = gv.exact_topk("ip", base, f(1, 2, 3), 2)       # array_inner_product.test:36-43 (negated)
+    assert list(ids[0]) == [2, 1] and list(dist[0]) == [-50.0, -17.0]
+
+
+@pytest.mark.parametrize("metric,d,n,nq,k", [("l2sq", 128, 50000, 333, 10), ("cosine", 768, 3000, 70, 10), ("ip", 96, 20000, 17, 100), ("l2sq", 3, 729, 5, 7)])
+def test_exact_topk_parity_against_checker(metric, d, n, nq, k):
+    import oracle
+    base, q = synth.clustered(n, d, 50, 8, 400 + d, nq) if d > 3 else (synth.readme_grid(), np.array([[1, 2, 3], [5, 5, 5], [9, 9, 9], [0, 0, 0], [4.5, 4.5, 4.5]], np.float32))
+    if oracle.have_ref():
+        from oracle import ref
+        want_ids, want_d = ref.duckdb_topk(metric, base, q, k, threads=8)
+    else:
+        from oracle import port
+        want_ids, want_d = port.exact_topk(metric, base, q, k)
+    ids, dist = gv.exact_topk(metric, base, q, k)
+    np.testing.assert_array_equal(ids, want_ids)
+    np.testing.assert_array_equal(dist.view(np.uint32), want_d.view(np.uint32))
+
+
+def test_exact_topk_key_mapping_and_small_inputs():
+    base = synth.readme_grid()
+    keys = np.arange(729, dtype=np.int64) * 10 + 5
+    ids, dist = gv.exact_topk("l2sq", base, np.array([[1, 2, 3]], np.float32), 3, keys=keys)
+    assert list(ids[0]) == [115, 25, 105]
+    ids, dist = gv.exact_topk("l2sq", base[:2], np.array([[1, 1, 1]], np.float32), 5)   # k > n: tail = -1 / inf
+    assert list(ids[0]) == [0, 1, -1, -1, -1] and np.isinf(dist[0][2:]).all()
+
+
+def test_merge_topk_orders_by_distance_then_key():
+    import torch
+    rng = np.random.default_rng(3)
+    shards, nq, k = 4, 50, 10
+    d = np.sort(rng.integers(0, 30, size=(shards, nq, k)).astype(np.float32), axis=2)   # many ties across shards
+    keys = rng.permutation(shards * nq * k).reshape(shards, nq, k).astype(np.int64)
+    d[3, :, 7:] = np.inf
+    keys[3, :, 7:] = -1                                                                  # a short list
+    gk, gd = torch.from_numpy(keys).cuda(), torch.from_numpy(d).cuda()
+    ok = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    od = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), shards, nq, k, ok.data_ptr(), od.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for qi in range(nq):
+        cand = sorted((float(d[s, qi, i]), int(keys[s, qi, i])) for s in range(shards) for i in range(k) if keys[s, qi, i] >= 0)[:k]
+        assert [c[1] for c in cand] == ok[qi].tolist()
+        assert [c[0] for c in cand] == od[qi].tolist()

@@ -1,0 +1,136 @@
+"""GPU parity #1: searching a reference-built (deserialised) graph through the C ABI returns the reference's row ids,
+distances (bit for bit) and traversal counters. Checker = compiled reference when present, else the pinned C port."""
+import numpy as np
+import pytest
+import duckdb_vss_b200 as gv
+from duckdb_vss_b200 import synth
+from conftest import golden_cases, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _load(z, blob):
+    ix = gv.Index(z["base"].shape[1], str(z["metric"]), M=int(z["M"]), M0=int(z["M0"]), ef_construction=int(z["efc"]))
+    ix.load(blob)
+    return ix
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_golden_search_identical_ids_distances_counters(name):
+    z, blob = load_golden(name)
+    ix = _load(z, blob)
+    assert ix.size() == z["base"].shape[0]
+    for ef in (3, 10, 64, 128):
+        keys, dist, counts, st = ix.ef_search(z["queries"], 10, ef, stats=True)
+        np.testing.assert_array_equal(keys, z[f"keys_ef{ef}"], err_msg=f"{name} ef={ef}")
+        np.testing.assert_array_equal(dist.view(np.uint32), z[f"dist_ef{ef}"].view(np.uint32))
+        np.testing.assert_array_equal(st["computed"], z[f"computed_ef{ef}"].astype(np.uint32))
+        np.testing.assert_array_equal(st["visited"], z[f"visited_ef{ef}"].astype(np.uint32))
+        assert (st["flags"] == 0).all()
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_stream_round_trip_is_byte_identical(name):
+    z, blob = load_golden(name)
+    ix = _load(z, blob)
+    assert ix.serialized_length() == len(blob)
+    assert ix.save() == blob
+
+
+def test_readme_known_answer_through_c_abi():
+    z, blob = load_golden("readme_l2sq")
+    ix = _load(z, blob)
+    keys, dist, counts = ix.ef_search(np.array([[1, 2, 3]], np.float32), 3, 64)
+    assert list(keys[0]) == [11, 92, 12]          # SURVEY §8c (compiled reference)
+    assert list(np.sqrt(dist[0])) == [0.0, 1.0, 1.0]  # hnsw_result.test:20-25
+    assert counts[0] == 3
+
+
+@pytest.mark.parametrize("metric,d,n,M", [("l2sq", 128, 20000, 16), ("cosine", 200, 6000, 16), ("ip", 96, 8000, 8), ("l2sq", 5, 3000, 3)])
+def test_reference_built_graph_search_parity(metric, d, n, M, checker):
+    Checker, kind = checker
+    base, q = synth.clustered(n, d, max(16, n // 100), 8, 100 + d, 300)
+    if metric == "ip":
+        base /= np.linalg.norm(base, axis=1, keepdims=True)
+    ref = Checker(d, metric, M=M)
+    ref.reserve(n, 8)
+    ref.add_bulk(base, threads=8)       # multi-threaded reference build; the saved graph is the shared input
+    blob = ref.save()
+    ix = gv.Index(d, metric, M=M)
+    ix.load(blob)
+    assert ix.save() == blob
+    for ef in (10, 64, 128):
+        want = ref.search_batch(q, 10, ef)
+        keys, dist, counts, st = ix.ef_search(q, 10, ef, stats=True)
+        np.testing.assert_array_equal(keys, want["keys"], err_msg=f"{metric} ef={ef} ({kind})")
+        np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32))
+        np.testing.assert_array_equal(counts, want["counts"])
+        np.testing.assert_array_equal(st["computed"], want["computed"].astype(np.uint32))
+        np.testing.assert_array_equal(st["visited"], want["visited"].astype(np.uint32))
+
+
+def test_removed_members_are_traversed_but_never_returned(checker):
+    Checker, _ = checker
+    n, d = 3000, 16
+    base, q = synth.clustered(n, d, 30, 6, 5, 100)
+    ref = Checker(d, "l2sq")
+    ref.reserve(n, 1)
+    ref.add_bulk(base)
+    ix = gv.Index(d, "l2sq")
+    ix.load(ref.save())
+    gone = list(range(0, n, 3))
+    for key in gone:
+        assert ref.remove(key) == 1
+        assert ix.remove(key) == 1
+    assert ix.remove(10 ** 9) == 0                      # unknown key: silent no-op (hnsw_index.cpp:478)
+    assert ix.size() == n - len(gone)
+    want = ref.search_batch(q, 10, 64)
+    keys, dist, counts = ix.ef_search(q, 10, 64)
+    np.testing.assert_array_equal(keys, want["keys"])
+    np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32))
+    assert not np.isin(keys, gone).any()
+    # removed slots survive a save/load cycle (hnsw_crud.test:12-47)
+    blob = ix.save()
+    assert blob == ref.save()
+    iy = gv.Index(d, "l2sq")
+    iy.load(blob)
+    assert iy.size() == n - len(gone)
+    k2, _, _ = iy.ef_search(q, 10, 64)
+    np.testing.assert_array_equal(k2, keys)
+
+
+def test_edge_cases():
+    z, blob = load_golden("readme_l2sq")
+    ix = _load(z, blob)
+    q = np.array([[1, 2, 3]], np.float32)
+    keys, dist, counts = ix.ef_search(q, 0, 64)           # k == 0 -> empty (index.hpp:2489-2490)
+    assert counts[0] == 0
+    keys, dist, counts = ix.ef_search(q, 1000, 64)        # k > N: beam = max(ef, k), returns <= N
+    assert counts[0] == 729 and len(set(keys[0][:729])) == 729 and (keys[0][729:] == -1).all()
+    assert (np.diff(dist[0][:729]) >= 0).all()
+    keys, dist, counts = ix.ef_search(q, 3, 0)            # ef == 0 -> 64 (index.hpp:2493-2494)
+    assert list(keys[0]) == [11, 92, 12]
+    nanq = np.full((2, 3), np.nan, np.float32)            # NULL outer row of the index join (hnsw_lateral_join.test:57-67)
+    keys, dist, counts = ix.ef_search(nanq, 3, 64)
+    assert (counts <= 3).all()
+    empty = gv.Index(3, "l2sq")                           # empty index -> 0 rows (hnsw_insert.test:18-21)
+    empty.reserve(32, 1)
+    keys, dist, counts = empty.ef_search(q, 3, 64)
+    assert counts[0] == 0 and (keys == -1).all()
+    assert empty.size() == 0 and len(empty.save()) == 8 + 64 + 40
+
+
+def test_device_resident_search_matches_host_path():
+    import torch
+    z, blob = load_golden("clustered16_l2sq")
+    ix = _load(z, blob)
+    q = torch.from_numpy(z["queries"]).cuda()
+    nq, k = q.shape[0], 10
+    keys = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    counts = torch.empty(nq, dtype=torch.int32, device="cuda")
+    ix.search_device(q.data_ptr(), nq, k, 64, keys.data_ptr(), dist.data_ptr(), counts.data_ptr(), 0,
+                     torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(keys.cpu().numpy(), z["keys_ef64"])
+    np.testing.assert_array_equal(dist.cpu().numpy().view(np.uint32), z["dist_ef64"].view(np.uint32))
