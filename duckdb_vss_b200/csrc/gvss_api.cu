@@ -10,6 +10,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <deque>
 #include <mutex>
 #include <string>
@@ -178,6 +179,8 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     p.queries = d_queries; p.nq = nq; p.k = k; p.limit = limit;
     p.keys_out = d_keys_out; p.dist_out = d_dist_out; p.counts_out = d_counts_out; p.stats_out = d_stats_out;
     p.entry = x->entry; p.max_level = x->max_level < 0 ? 0 : x->max_level;
+    p.trace_query = -1;
+    if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
     p.sl = make_scratch_layout(limit);
     const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * limit, 256), 2048);
     p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), heap_smem, 0);
@@ -783,12 +786,14 @@ static int flush_locked(gvss_index *x) {
     unsigned long long es = x->max_level < 0 ? ~0ull : (((unsigned long long)(uint32_t)x->max_level << 32) | x->entry);
     CU(cudaMemcpyAsync(x->d_entry_state, &es, 8, cudaMemcpyHostToDevice, x->stream));
     uint64_t linked = x->count - 0; // nodes already in the graph
+    uint64_t ramp = 256; // in-flight inserts <= 1/256 of the linked nodes: recall within 0.005 of a sequential build (profiles/build_ramp_r1.txt)
+    if (const char *e = getenv("GVSS_BUILD_RAMP")) ramp = std::max<uint64_t>(1, strtoull(e, nullptr, 10));
     uint64_t done = 0;
     const uint64_t total = slots.size();
     const int metric = metric_id(x->cfg.metric);
     while (done < total) {
         const uint64_t have = linked + done;
-        uint64_t conc = std::max<uint64_t>(1, have / 16);
+        uint64_t conc = std::max<uint64_t>(1, have / ramp);
         conc = std::min<uint64_t>(conc, max_warps);
         uint64_t len = conc >= max_warps ? total - done : std::max<uint64_t>(conc * 2, 16);
         len = std::min(len, total - done);

@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #ifndef GVSS_USE_TMA
 #define GVSS_USE_TMA 1
@@ -65,7 +66,7 @@ struct WarpWs {
 
 struct Counters {
     uint32_t computed, cycles, base;
-    uint32_t flags;
+    uint32_t flags; // bit0: visited table / queue overflow; bit31: trace this query (debug aid, GVSS_TRACE_QUERY)
 };
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
@@ -245,8 +246,9 @@ __device__ __forceinline__ bool vis_insert(WarpWs &w, uint32_t key) {
 
 // ---------------------------------------------------------------------------------------------------------
 // candidate queue: binary heap with usearch's shift_up / shift_down (index.hpp:624-644). The reference keeps
-// {-distance, slot} in a max-heap; here +distance in a min-heap with every comparison mirrored. All lanes run
-// the same scalar code on broadcast shared-memory reads, so no shuffles or barriers are needed.
+// {-distance, slot} in a max-heap; here +distance in a min-heap with every comparison mirrored. Lane 0 is the single
+// writer (lanes of a warp are not guaranteed to run in lockstep, so redundant all-lane writes could land out of order);
+// the other lanes see the result after the __syncwarp() that ends each operation.
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ Cand heap_get(const WarpWs &w, uint32_t i) {
     return i < w.heap_smem ? w.heap[i] : w.heap_ovf[i - w.heap_smem];
@@ -256,34 +258,40 @@ __device__ __forceinline__ void heap_set(WarpWs &w, uint32_t i, Cand v) {
 }
 __device__ __forceinline__ bool heap_push(WarpWs &w, uint32_t &size, float d, uint32_t s) {
     if (size >= w.heap_total) return false;
-    uint32_t i = size++;
-    while (i) {
-        const uint32_t p = (i - 1) >> 1;
-        const Cand pe = heap_get(w, p);
-        if (!(pe.d > d)) break; // less(parent, child) on negated distances
-        heap_set(w, i, pe);
-        i = p;
+    if (lane_id() == 0) {
+        uint32_t i = size;
+        while (i) {
+            const uint32_t p = (i - 1) >> 1;
+            const Cand pe = heap_get(w, p);
+            if (!(pe.d > d)) break; // less(parent, child) on negated distances
+            heap_set(w, i, pe);
+            i = p;
+        }
+        heap_set(w, i, Cand{d, s});
     }
-    heap_set(w, i, Cand{d, s});
+    size++;
+    __syncwarp();
     return true;
 }
 __device__ __forceinline__ void heap_pop(WarpWs &w, uint32_t &size) {
     size--;
-    if (size == 0) return;
-    const Cand x = heap_get(w, size);
-    uint32_t i = 0;
-    for (;;) {
-        uint32_t mx = i;
-        float best = x.d;
-        const uint32_t l = 2 * i + 1, r = 2 * i + 2;
-        Cand le, re;
-        if (l < size) { le = heap_get(w, l); if (best > le.d) { mx = l; best = le.d; } }
-        if (r < size) { re = heap_get(w, r); if (best > re.d) { mx = r; } }
-        if (mx == i) break;
-        heap_set(w, i, mx == l ? le : re);
-        i = mx;
+    if (size && lane_id() == 0) {
+        const Cand x = heap_get(w, size);
+        uint32_t i = 0;
+        for (;;) {
+            uint32_t mx = i;
+            float best = x.d;
+            const uint32_t l = 2 * i + 1, r = 2 * i + 2;
+            Cand le = x, re = x;
+            if (l < size) { le = heap_get(w, l); if (best > le.d) { mx = l; best = le.d; } }
+            if (r < size) { re = heap_get(w, r); if (best > re.d) { mx = r; } }
+            if (mx == i) break;
+            heap_set(w, i, mx == l ? le : re);
+            i = mx;
+        }
+        heap_set(w, i, x);
     }
-    heap_set(w, i, x);
+    __syncwarp();
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -407,6 +415,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         heap_pop(w, heap_size);
         cnt.cycles++;
         cnt.base++;
+        if ((cnt.flags & 0x80000000u) && lane == 0)
+            printf("pop %u slot %u d %.9g radius %.9g heap %u top %u computed %u\n", cnt.base, c.s, c.d, radius, heap_size, top_size, cnt.computed);
         if (INSERT && c.s == new_slot) continue;
 
         uint32_t cap;

@@ -35,6 +35,7 @@ struct SearchParams {
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;
+    long long trace_query; // -1 = off
 };
 // grid = number of resident warps; returns cudaError
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);

@@ -50,7 +50,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = i < g.dims ? __ldg(qsrc + i) : 0.0f;
         __syncwarp();
 
-        Counters cnt = {0, 0, 0, 0};
+        Counters cnt = {0, 0, 0, (long long)qi == p.trace_query ? 0x80000000u : 0u};
         uint32_t top_size = 0;
         if (g.count && p.k) {
             const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
@@ -64,7 +64,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
         }
         if (lane == 0) {
             if (p.counts_out) p.counts_out[qi] = n;
-            if (p.stats_out) p.stats_out[qi] = gvss_search_stats{cnt.computed, cnt.cycles, cnt.base, cnt.flags};
+            if (p.stats_out) p.stats_out[qi] = gvss_search_stats{cnt.computed, cnt.cycles, cnt.base, cnt.flags & 0x7FFFFFFFu};
         }
         __syncwarp();
     }

@@ -17,6 +17,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <stdio.h>
+static int g_trace = 0;
+void orc_set_trace(int on) { g_trace = on; }
 #define FREE_KEY INT64_MAX /* index_dense.hpp: free_key_ = default_free_value<vector_key_t>() */
 
 typedef struct { float distance; uint32_t slot; } cand_t; /* index.hpp:1805-1809, ordered by distance only */
@@ -220,6 +223,7 @@ static void search_base(orc_index *x, const float *q, uint64_t start, uint64_t l
         cand_t c = x->next[0];
         if ((-c.distance) > radius) break;
         next_pop(x); x->cycles++; if (hops) (*hops)++;
+        if (g_trace) printf("pop %llu slot %u d %.9g radius %.9g heap %llu top %llu computed %llu\n", hops ? (unsigned long long)*hops : 0ull, c.slot, -c.distance, radius, (unsigned long long)x->next_size, (unsigned long long)x->top_size, (unsigned long long)x->computed);
         uint32_t *nb = nbrs(x, c.slot, 0); uint32_t cnt = nb[0];
         for (uint32_t j = 0; j < cnt; j++) {
             uint32_t s = nb[1 + j];

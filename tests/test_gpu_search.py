@@ -91,7 +91,14 @@ def test_removed_members_are_traversed_but_never_returned(checker):
     assert not np.isin(keys, gone).any()
     # removed slots survive a save/load cycle (hnsw_crud.test:12-47)
     blob = ix.save()
-    assert blob == ref.save()
+    want_blob = ref.save()
+    # the only bytes allowed to differ are count_present / count_deleted in the 64-byte header: the reference derives
+    # them from its free-slot ring, whose size() wraps to 0 whenever the ring is exactly full (1000 removes -> it
+    # reports 2960 present / 40 deleted); gvss writes the true counts. Loaders ignore both fields.
+    off = 8 + n * d * 4 + 17
+    assert blob[:off] == want_blob[:off] and blob[off + 16:] == want_blob[off + 16:]
+    assert int.from_bytes(blob[off:off + 8], "little") == n - len(gone)
+    assert int.from_bytes(blob[off + 8:off + 16], "little") == len(gone)
     iy = gv.Index(d, "l2sq")
     iy.load(blob)
     assert iy.size() == n - len(gone)
