@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the HNSW hot path (BASELINE.json: "HNSW search QPS at recall@10>=0.95 (batched) +
+index build vectors/sec" on configs[1] = 1M x FLOAT[128] l2sq, 10k-query batch, k=10).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl gvss|reference]
+
+A step = one batched search of the 10 000-query batch (k=10) at the smallest ef of the sweep that reaches
+recall@10 >= 0.95 on the GPU-built graph. `value` is device-timed with queries and index resident in HBM; `e2e` is
+the same batch through the host-pointer C-ABI call (gvss_search: H2D of the queries + kernel + D2H of the results
+inside the timed region). The bulk build (gvss_add_batch_device + gvss_flush) is timed once, before the steps, and
+reported under "build". N > 1: one process per GPU, every rank owns an independent 1M-vector shard (own sub-graph, no
+build-time communication); every query is searched on every shard, per-shard top-k lists are all-gathered over NCCL
+and merged on the device (weak scaling: per-GPU work is fixed).
+
+`--impl reference` times the UNMODIFIED reference (vendored usearch via oracle/_ref, else the pinned C port) on the
+host cores on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "hnsw_search_qps_at_recall10_ge_0.95"
+EF_SWEEP = (16, 32, 64, 128, 192, 256, 384, 512)
+# with the usearch defaults (M=16, efc=128) recall@10 >= 0.95 is NOT reachable on the 1M set within
+# ef <= 512 (reference-built graph: 0.80 at ef=512, profiles/recall_1m_r1.txt), so both arms use M=32 / ef_construction=200.
+M_BENCH, M0_BENCH, EFC_BENCH = 32, 64, 200
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy bandwidth)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def algorithmic_bytes(stats, d, M, M0, k):
+    """B_q = C_q*4d + H0_q*(4+4*M0) + Hup_q*(4+4*M) + 12k, from usearch-compatible counters."""
+    c = stats[:, 0].astype(np.float64).sum()
+    h0 = stats[:, 2].astype(np.float64).sum()
+    hup = (stats[:, 1].astype(np.float64) - stats[:, 2].astype(np.float64)).sum()
+    return c * 4 * d + h0 * (4 + 4 * M0) + hup * (4 + 4 * M) + stats.shape[0] * 12.0 * k
+
+
+def run_reference(args):
+    """CPU arm: the reference's own usearch path on the host cores (bounded sample)."""
+    import oracle
+    from duckdb_vss_b200 import synth
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    if oracle.have_ref():
+        from oracle import ref as impl
+        kind, Index, threads = "reference", impl.RefIndex, impl.hardware_threads()
+    else:
+        oracle.build()
+        from oracle import port as impl
+        kind, Index, threads = "port", impl.PortIndex, 1
+    n_sample = args.ref_n or min(args.n, max(20000, 1500 * threads))
+    nq = min(args.nq, 2000 if kind == "reference" else 200)
+    base, q = synth.clustered(n_sample, args.dims, max(1024, n_sample // 100), 16, 42, nq)
+    ix = Index(args.dims, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
+    ix.reserve(n_sample, threads)
+    t0 = time.perf_counter()
+    ix.add_bulk(base, threads=threads)
+    t_build = time.perf_counter() - t0
+    truth = None
+    if kind == "reference":
+        truth, _ = impl.duckdb_topk("l2sq", base, q[:200], 10, threads=threads)
+    ef, recall = args.ef or 128, None
+    if truth is not None and not args.ef:
+        for e in EF_SWEEP:
+            r = synth.recall_at_k(ix.search_batch(q[:200], 10, e, threads=threads)["keys"], truth)
+            ef, recall = e, r
+            if r >= 0.95:
+                break
+    for _ in range(args.warmup):
+        ix.search_batch(q, 10, ef, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ix.search_batch(q, 10, ef, threads=threads)
+    dt = time.perf_counter() - t0
+    qps = nq * args.steps / dt
+    sample = f"index over the first {n_sample} of {args.n} vectors built by {threads} host threads; {nq} of {args.nq} queries per step; ef={ef}"
+    line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "1M x FLOAT[128] l2sq (SIFT-1M shape), 10k-query batch, k=10", "ef_search": ef,
+                       "recall_at_10": recall, "M": M_BENCH, "M0": M0_BENCH, "ef_construction": EFC_BENCH},
+            "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": kind, "sample": sample,
+                             "build_vectors_per_s": n_sample / t_build},
+            "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "build": {"value": n_sample / t_build, "unit": "vectors/s", "vectors": n_sample, "seconds": t_build}}
+    print(json.dumps(line))
+
+
+def cpu_baseline(args, blob_getter, q, ef, truth):
+    """Reference usearch (oracle/_ref) on the host cores: search on the SAME (GPU-built) graph, build on a bounded sample."""
+    try:
+        import oracle
+        if oracle.have_ref():
+            from oracle import ref as impl
+            kind, threads = "reference", impl.hardware_threads()
+            Index = impl.RefIndex
+        else:
+            if not oracle.have_port():
+                oracle.build()
+            from oracle import port as impl
+            kind, threads, Index = "port", 1, impl.PortIndex
+        from duckdb_vss_b200 import synth
+        ix = Index(args.dims, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
+        t0 = time.perf_counter()
+        ix.load(blob_getter())
+        t_load = time.perf_counter() - t0
+        nq = q.shape[0] if kind == "reference" else min(q.shape[0], 300)
+        ix.search_batch(q[:min(nq, 512)], 10, ef, threads=threads)  # warm
+        t0 = time.perf_counter()
+        r = ix.search_batch(q[:nq], 10, ef, threads=threads)
+        dt = time.perf_counter() - t0
+        rec = synth.recall_at_k(r["keys"], truth[:nq])
+        # build sample: first min(n, 2500*T) vectors with the extension's thread pattern
+        nb = min(args.n, max(20000, 1500 * threads)) if kind == "reference" else 3000
+        base_s, _ = synth.clustered(nb, args.dims, max(1024, nb // 100), 16, 42, 0)
+        b = Index(args.dims, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
+        b.reserve(nb, threads)
+        t0 = time.perf_counter()
+        b.add_bulk(base_s, threads=threads)
+        tb = time.perf_counter() - t0
+        return {"value": nq / dt, "unit": "queries/s", "cores": threads, "kind": kind,
+                "sample": f"{nq} queries, ef={ef}, on the GPU-built 1M graph loaded from its usearch stream (load {t_load:.1f}s); "
+                          f"build timed on the first {nb} vectors", "recall_at_10": rec,
+                "build_vectors_per_s": nb / tb}
+    except Exception as e:  # the baseline must never take the product number down
+        return {"value": None, "unit": "queries/s", "cores": 0, "kind": "unavailable", "sample": repr(e)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="gvss", choices=["gvss", "reference"])
+    ap.add_argument("--n", type=int, default=1_000_000)
+    ap.add_argument("--nq", type=int, default=10_000)
+    ap.add_argument("--dims", type=int, default=128)
+    ap.add_argument("--ef", type=int, default=0, help="0 = smallest ef of the sweep with recall@10 >= 0.95")
+    ap.add_argument("--ref-n", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "gvss" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import duckdb_vss_b200 as gv
+    from duckdb_vss_b200 import synth, index as gvi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    d, n, nq, k, M, M0 = args.dims, args.n, args.nq, 10, M_BENCH, M0_BENCH
+    # per-rank shard: same law, shard-specific seed; the query batch is identical on every rank (seed 43 stream of rank 0)
+    base_np, q_np = synth.clustered(n, d, max(1024, n // 100), 16, 42 + 1000 * rank, 0)
+    _, q_np = synth.clustered(1, d, max(1024, n // 100), 16, 42, nq)
+    base = torch.from_numpy(base_np).to(dev)
+    q = torch.from_numpy(q_np).to(dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    # ---- bulk build (timed once): rows already in HBM -> graph ------------------------------------------------
+    ix = gv.Index(d, "l2sq", M=M, M0=M0, ef_construction=EFC_BENCH, ef_search=64, device=local)
+    ix.reserve(n, 1)
+    keys_np = np.arange(n, dtype=np.int64) + rank * n
+    torch.cuda.synchronize()
+    l0 = gv.lib().gvss_kernel_launches()
+    t0 = time.perf_counter()
+    ix.add_batch_device(base.data_ptr(), n, keys=keys_np)
+    ix.flush()
+    torch.cuda.synchronize()
+    t_build = time.perf_counter() - t0
+    build_launches = gv.lib().gvss_kernel_launches() - l0
+
+    # ---- ground truth (exact kernel, parity-checked against DuckDB's folds) and ef selection -------------------
+    truth = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    tdist = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    kdev = torch.from_numpy(keys_np).to(dev)
+    t0 = time.perf_counter()
+    gvi.exact_topk_device("l2sq", base.data_ptr(), n, q.data_ptr(), nq, d, k, truth.data_ptr(), tdist.data_ptr(), kdev.data_ptr(), stream)
+    torch.cuda.synchronize()
+    t_exact = time.perf_counter() - t0
+    truth_np = truth.cpu().numpy()
+
+    okeys = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    odist = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    ocnt = torch.empty(nq, dtype=torch.int32, device=dev)
+    ostat = torch.zeros((nq, 4), dtype=torch.int32, device=dev)
+
+    def search(ef, stats=False):
+        ix.search_device(q.data_ptr(), nq, k, ef, okeys.data_ptr(), odist.data_ptr(), ocnt.data_ptr(),
+                         ostat.data_ptr() if stats else 0, stream)
+
+    sweep = {}
+    ef = args.ef
+    for e in ([args.ef] if args.ef else EF_SWEEP):
+        search(e)
+        torch.cuda.synchronize()
+        r = synth.recall_at_k(okeys.cpu().numpy(), truth_np)
+        sweep[e] = round(r, 4)
+        ef = e
+        if r >= 0.95:
+            break
+    recall = sweep[ef]
+    search(ef, stats=True)
+    torch.cuda.synchronize()
+    st = ostat.cpu().numpy().view(np.uint32)
+    algo_bytes = algorithmic_bytes(st, d, M, M0, k)
+
+    # multi-GPU exchange: all-gather of the per-shard lists (12*nq*k bytes per rank) + device merge
+    if world > 1:
+        gk = torch.empty((world, nq, k), dtype=torch.int64, device=dev)
+        gd = torch.empty((world, nq, k), dtype=torch.float32, device=dev)
+        mk = torch.empty((nq, k), dtype=torch.int64, device=dev)
+        md = torch.empty((nq, k), dtype=torch.float32, device=dev)
+
+    def step():
+        search(ef)
+        if world > 1:
+            dist.all_gather_into_tensor(gk, okeys)
+            dist.all_gather_into_tensor(gd, odist)
+            gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, mk.data_ptr(), md.data_ptr(), stream)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = gv.lib().gvss_kernel_launches()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        t_wall0 = time.perf_counter()
+        for a, b, c in ev:
+            a.record()
+            search(ef)
+            b.record()
+            if world > 1:
+                dist.all_gather_into_tensor(gk, okeys)
+                dist.all_gather_into_tensor(gd, odist)
+                gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, mk.data_ptr(), md.data_ptr(), stream)
+            c.record()
+        torch.cuda.synchronize()
+        t_wall = time.perf_counter() - t_wall0
+    launches = gv.lib().gvss_kernel_launches() - l0
+    t_dev = sum(a.elapsed_time(c) for a, b, c in ev) / 1e3           # whole steps, device time
+    t_kernel = sum(a.elapsed_time(b) for a, b, c in ev) / 1e3 / args.steps  # search launch alone (roofline)
+    if world > 1:
+        tt = torch.tensor([t_dev], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_dev = float(tt.item())
+        dist.barrier()
+    merged_recall = None
+    if world > 1:
+        merged_recall = "n/a (per-shard ground truth only)"
+
+    # ---- e2e through the host-pointer C-ABI call (pinned host buffers; H2D + kernel + D2H inside the timed region) --
+    qh = torch.from_numpy(q_np).pin_memory()
+    kh = torch.empty((nq, k), dtype=torch.int64).pin_memory()
+    dh = torch.empty((nq, k), dtype=torch.float32).pin_memory()
+    ch = torch.empty(nq, dtype=torch.int32).pin_memory()
+
+    def e2e_step():
+        gv.capi.check(gv.lib().gvss_search(ix._h, ctypes.c_void_p(qh.data_ptr()), nq, k, ef, ctypes.c_void_p(kh.data_ptr()),
+                                           ctypes.c_void_p(dh.data_ptr()), ctypes.c_void_p(ch.data_ptr()), None))
+    for _ in range(3):
+        e2e_step()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    t_e2e = time.perf_counter() - t0
+    if world > 1:
+        tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_e2e = float(tt.item())
+    e2e_recall = synth.recall_at_k(kh.numpy(), truth_np)
+    h2d = nq * d * 4
+    d2h = nq * k * 12 + nq * 4 + nq * 16
+
+    build_vps = n / t_build
+    if world > 1:
+        tt = torch.tensor([t_build], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        build_vps = world * n / float(tt.item())
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = algo_bytes / t_kernel / 1e9
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            cpu = cpu_baseline(args, ix.save, q_np, ef, truth_np)
+        units = world * nq * args.steps
+        line = {
+            "metric": METRIC, "value": units / t_dev, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "1M x FLOAT[128] l2sq (SIFT-1M shape) per GPU, 10k-query batch, k=10",
+                       "generator": "clustered(C=N/100, r=16) seed 42 (SURVEY.md App. D law, numpy)", "n_per_gpu": n,
+                       "queries_per_step": nq, "k": k, "ef_search": ef, "recall_at_10": recall, "ef_sweep": sweep,
+                       "M": M, "M0": M0, "ef_construction": EFC_BENCH,
+                       "units": "per-shard query searches summed over ranks (every query visits every shard)",
+                       "global_queries_per_s": nq * args.steps / t_dev,
+                       "l2_policy": "inputs larger than L2: 512 MB vectors + 128 MB adjacency per GPU vs 126 MB L2; no flush",
+                       "parallelism": f"shard{world}" if world > 1 else "single"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "k_search<l2sq>",
+                         "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": 1e3 * t_kernel},
+            "cpu_baseline": cpu,
+            "e2e": {"value": world * nq * args.steps / t_e2e, "unit": "queries/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "recall_at_10": e2e_recall, "api": "gvss_search (host pointers)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks.summary(),
+            "build": {"value": build_vps, "unit": "vectors/s", "seconds": t_build, "kernel_launches": int(build_launches),
+                      "note": "gvss_add_batch_device + gvss_flush, rows resident in HBM, timed once before the steps"},
+            "exact_topk": {"seconds": t_exact, "queries": nq, "base": n, "note": "ground truth, first call (includes lazy module load)"},
+            "wall_s_timed_region": t_wall,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

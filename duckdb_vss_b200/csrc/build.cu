@@ -31,6 +31,9 @@ __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, cons
     w.vis_limit = sl.vis_limit;
     w.heap_ovf = reinterpret_cast<Cand *>(base + (size_t)sl.vis_slots * 4);
     w.heap_total = sm.heap_smem + sl.heap_ovf;
+    w.bitmap = reinterpret_cast<uint32_t *>(base + (size_t)sl.vis_slots * 4 + (size_t)sl.heap_ovf * 8);
+    w.bitmap_words = sl.bitmap_words;
+    w.use_bitmap = false;
     w.phase[0] = w.phase[1] = 0;
     if (lane_id() == 0) {
         mbar_init(&w.mbar[0], 1);
@@ -140,6 +143,12 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         for (int l = min(level, max_level); l >= 0; --l) {
             uint32_t top_size = 0;
             beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
+            if (cnt.flags & 1u) { // visited table would have overfilled: redo the level with the exact bitmap
+                cnt.flags = 0;
+                w.use_bitmap = true;
+                beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
+                w.use_bitmap = false;
+            }
 
             // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)
             const uint32_t cap_l = l ? g.M : g.M0;

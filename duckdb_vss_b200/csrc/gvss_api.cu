@@ -181,7 +181,7 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     p.entry = x->entry; p.max_level = x->max_level < 0 ? 0 : x->max_level;
     p.trace_query = -1;
     if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
-    p.sl = make_scratch_layout(limit);
+    p.sl = make_scratch_layout(limit, x->count);
     const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * limit, 256), 2048);
     p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), heap_smem, 0);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
@@ -409,7 +409,7 @@ int gvss_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, ui
     CU(cudaStreamSynchronize(x->stream));
     // a query whose visited table would have passed 75 % load was cut short: the synchronous path cannot return it
     for (uint64_t i = 0; i < nq; i++)
-        if (st[i].flags & 1u) return fail("gvss_search: visited table overflow on query %llu (beam %u)", (unsigned long long)i, std::max(ef ? ef : 64u, k));
+        if (st[i].flags & 1u) return fail("gvss_search: candidate queue overflow on query %llu (beam %u)", (unsigned long long)i, std::max(ef ? ef : 64u, k));
     return 0;
 }
 
@@ -776,7 +776,7 @@ static int flush_locked(gvss_index *x) {
     p.ef_add = x->cfg.expansion_add;
     const uint32_t cmax = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
-    p.sl = make_scratch_layout(std::max(p.ef_add, cmax));
+    p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
     const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * p.ef_add, 256), 2048);
     p.sm = make_smem_layout(x->dpad, top_cap, heap_smem, (2 * cmax + 2) * 8);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);

@@ -60,6 +60,9 @@ struct WarpWs {
     uint32_t heap_smem, heap_total;
     uint32_t *vis;       // visited table (open addressing) in global scratch
     uint32_t vis_mask, vis_limit;
+    uint32_t *bitmap;    // exact fallback: one bit per node, used when a search would overfill the table
+    uint32_t bitmap_words;
+    bool use_bitmap;
     uint64_t *mbar;      // 2 mbarriers (one per stage buffer)
     uint32_t phase[2];
 };
@@ -226,14 +229,24 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
 // usearch's growing_hash_set_gt, index.hpp:852-970 — only membership matters)
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void vis_clear(WarpWs &w) {
-    uint4 *p = reinterpret_cast<uint4 *>(w.vis);
-    const uint32_t n4 = (w.vis_mask + 1) / 4;
-    const uint4 e = make_uint4(kInvalid, kInvalid, kInvalid, kInvalid);
-    for (uint32_t i = lane_id(); i < n4; i += 32) p[i] = e;
+    if (w.use_bitmap) {
+        uint4 *p = reinterpret_cast<uint4 *>(w.bitmap);
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (uint32_t i = lane_id(); i < w.bitmap_words / 4; i += 32) p[i] = z;
+    } else {
+        uint4 *p = reinterpret_cast<uint4 *>(w.vis);
+        const uint32_t n4 = (w.vis_mask + 1) / 4;
+        const uint4 e = make_uint4(kInvalid, kInvalid, kInvalid, kInvalid);
+        for (uint32_t i = lane_id(); i < n4; i += 32) p[i] = e;
+    }
     __syncwarp();
 }
 // returns true when `key` was not yet present (and is now)
 __device__ __forceinline__ bool vis_insert(WarpWs &w, uint32_t key) {
+    if (w.use_bitmap) {
+        const uint32_t bit = 1u << (key & 31u);
+        return (atomicOr(&w.bitmap[key >> 5], bit) & bit) == 0u;
+    }
     uint32_t h = (key * 2654435761u) >> 7;
     for (;;) {
         h &= w.vis_mask;
@@ -430,9 +443,10 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const uint32_t same = __match_any_sync(kFull, s);
             const bool leader = valid && (uint32_t)(__ffs(same) - 1) == lane;
             bool isnew = false;
-            if (leader && nvis < w.vis_limit) isnew = vis_insert(w, s);
+            const bool room = w.use_bitmap || nvis < w.vis_limit;
+            if (leader && room) isnew = vis_insert(w, s);
             const uint32_t nmask = __ballot_sync(kFull, isnew);
-            if (nvis >= w.vis_limit && __ballot_sync(kFull, leader)) cnt.flags |= 1u;
+            if (!room && __ballot_sync(kFull, leader)) cnt.flags |= 1u;
             if (!nmask) continue;
             nvis += __popc(nmask);
             cnt.computed += __popc(nmask);

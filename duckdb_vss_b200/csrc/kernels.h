@@ -16,10 +16,10 @@ SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem,
 
 // global scratch of one warp: visited table (vis_slots u32) followed by the queue overflow (heap_ovf Cand)
 struct ScratchLayout {
-    uint32_t vis_slots, vis_limit, heap_ovf;
+    uint32_t vis_slots, vis_limit, heap_ovf, bitmap_words;
     size_t bytes_per_warp;
 };
-ScratchLayout make_scratch_layout(uint32_t beam);
+ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes);
 
 struct SearchParams {
     const float *queries;

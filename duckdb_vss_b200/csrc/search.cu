@@ -24,6 +24,9 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
     w.vis_limit = sl.vis_limit;
     w.heap_ovf = reinterpret_cast<Cand *>(base + (size_t)sl.vis_slots * 4);
     w.heap_total = sm.heap_smem + sl.heap_ovf;
+    w.bitmap = reinterpret_cast<uint32_t *>(base + (size_t)sl.vis_slots * 4 + (size_t)sl.heap_ovf * 8);
+    w.bitmap_words = sl.bitmap_words;
+    w.use_bitmap = false;
     w.phase[0] = w.phase[1] = 0;
     if (lane_id() == 0) {
         mbar_init(&w.mbar[0], 1);
@@ -54,7 +57,15 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
         uint32_t top_size = 0;
         if (g.count && p.k) {
             const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            const Counters before = cnt;
             beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
+            if (cnt.flags & 1u) { // the hashed visited table would have overfilled: redo the level with the exact bitmap
+                cnt = before;
+                w.use_bitmap = true;
+                beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
+                w.use_bitmap = false;
+                cnt.flags |= 2u;
+            }
         }
         const uint32_t n = min(top_size, p.k); // top.shrink(wanted), index.hpp:2526-2527
         for (uint32_t i = lane; i < p.k; i += 32) {
@@ -93,7 +104,7 @@ SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem,
     return s;
 }
 
-ScratchLayout make_scratch_layout(uint32_t beam) {
+ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes) {
     // visited members per search ~ 20*beam + 500 on the measured data sets; 64*beam slots
     // (min 4096) keep the table under ~40 % load, the kernel flags a query that would exceed 75 %.
     ScratchLayout s{};
@@ -103,8 +114,9 @@ ScratchLayout make_scratch_layout(uint32_t beam) {
     while (v < want) v <<= 1;
     s.vis_slots = v;
     s.vis_limit = v / 4 * 3 - 32;
-    s.heap_ovf = v; // every queue entry was a newly visited node, so the queue can never outgrow the table
-    s.bytes_per_warp = (size_t)v * 4 + (size_t)s.heap_ovf * 8;
+    s.heap_ovf = v; // every queue entry was a newly visited node, so the queue cannot outgrow the hashed table
+    s.bitmap_words = (uint32_t)((nodes + 127) / 128 * 4);
+    s.bytes_per_warp = (size_t)v * 4 + (size_t)s.heap_ovf * 8 + (size_t)s.bitmap_words * 4;
     return s;
 }
 

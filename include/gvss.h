@@ -67,7 +67,8 @@ typedef struct gvss_search_stats {
     uint32_t computed_distances; /* context_t::computed_distances_count delta */
     uint32_t visited_members;    /* context_t::iteration_cycles delta = level-0 expansions + upper-level hops */
     uint32_t base_expansions;    /* level-0 expansions only */
-    uint32_t flags;              /* bit0: visited-table overflow (query was re-run with a larger table) */
+    uint32_t flags;              /* bit1: hashed visited table overfilled, level 0 redone with the exact bitmap (results exact);
+                                    bit0: candidate queue overflow (results of this query are not reliable) */
 } gvss_search_stats;
 
 /* --- lifetime ----------------------------------------------------------------------------------------------- */
