@@ -1,0 +1,27 @@
+"""GPU: the C++ drop-in shim (duckdb_vss_b200/shim/usearch/duckdb_usearch.hpp) driven with the extension's own call
+patterns (tests/cpp/shim_driver.cpp cites each call site). Compiles with g++ against include/gvss.h + libgvss.so."""
+import os
+import re
+import subprocess
+import pytest
+from duckdb_vss_b200 import capi
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_shim_driver_behaves_like_the_reference_index(tmp_path):
+    exe = str(tmp_path / "shim_driver")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", f"-I{ROOT}/include", f"-I{ROOT}/duckdb_vss_b200/shim",
+                    f"{ROOT}/tests/cpp/shim_driver.cpp", f"-L{libdir}", "-lgvss", f"-Wl,-rpath,{libdir}", "-o", exe], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True, timeout=120).stdout
+    print(out)
+    assert 'add_failures 0 size 729 capacity 729 over_capacity_error "Reserve capacity ahead of insertions!"' in out
+    m = re.search(r"scan 3: (\d+)/0 (\d+)/1 (\d+)/1", out)          # hnsw_result.test:20-25 (squared distances 0, 1, 1)
+    assert m and m.group(1) == "11"
+    assert "removed 1 size 728" in out and "level0_nodes 729" in out and "dims 3 metric e" in out
+    assert "removed_key_returned 0" in out and "compact_ok 1" in out
+    m = re.search(r"stream_bytes (\d+) serialized_length (\d+) load_ok 1 reloaded_size 728 same_results 1", out)
+    assert m and m.group(1) == m.group(2)
+    assert "after_reset_size 0" in out
