@@ -52,6 +52,8 @@ SIGNATURES = {
                               C.c_void_p, C.c_void_p]),
     "gvss_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gvss_search_device_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p,
+                                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gvss_save": (C.c_int, [C.c_void_p, WRITE_CB, C.c_void_p]),
     "gvss_load": (C.c_int, [C.c_void_p, READ_CB, C.c_void_p]),
     "gvss_serialized_length": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),

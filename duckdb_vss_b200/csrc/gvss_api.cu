@@ -378,6 +378,37 @@ int gvss_search_device(gvss_index *x, const float *queries, uint64_t nq, uint32_
     return search_device_locked(x, queries, nq, k, ef, keys_out, dist_out, counts_out, stats_out, (cudaStream_t)cuda_stream);
 }
 
+int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, uint32_t ef, int64_t *keys_out,
+                               float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out, void *cuda_stream) {
+    if (!x) return fail("null index");
+    if (nq && (!queries || !keys_out)) return fail("gvss_search_device_noalloc: null buffer");
+    std::lock_guard<std::mutex> lk(x->mu);
+    cudaSetDevice(x->device);
+    // inserting staged rows allocates; this entry point never does
+    if (x->staged.load()) return fail("gvss_search_device_noalloc: rows are staged; call gvss_flush first (it allocates, this call must not)");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (!nq) return 0;
+    if (!k) { if (counts_out) CU(cudaMemsetAsync(counts_out, 0, nq * 4, st)); return 0; }
+    if (!ef) ef = 64;
+    const uint32_t limit = std::max(ef, k);
+    if (limit > 16384) return fail("gvss: ef/k above 16384 not supported");
+    SearchParams p{};
+    p.queries = queries; p.nq = nq; p.k = k; p.limit = limit;
+    p.keys_out = keys_out; p.dist_out = dist_out; p.counts_out = counts_out; p.stats_out = stats_out;
+    p.entry = x->entry; p.max_level = x->max_level < 0 ? 0 : x->max_level;
+    p.trace_query = -1;
+    p.sl = make_scratch_layout(limit, x->count);
+    const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * limit, 256), 2048);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), heap_smem, 0);
+    const uint32_t resident = resident_warps(x->device, p.sm.bytes, false);
+    if (!resident) return fail("gvss: no CUDA device");
+    char err[384];
+    err[0] = 0;
+    if (launch_search_static_scratch(metric_id(x->cfg.metric), x->device, view_of(x), p, resident, st, err, sizeof err) != cudaSuccess)
+        return fail("%s", err);
+    return 0;
+}
+
 int gvss_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, uint32_t ef, int64_t *keys_out,
                 float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out) {
     if (!x) return fail("null index");

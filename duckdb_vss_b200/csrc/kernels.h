@@ -39,6 +39,12 @@ struct SearchParams {
 };
 // grid = number of resident warps; returns cudaError
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);
+// size of the built-in scratch array behind gvss_search_device_noalloc (held by every GPU that loads the library)
+#define GVSS_STATIC_SCRATCH_BYTES (64u << 20)
+// largest scratch one query slot may need there (so that at least 63 queries are always in flight)
+#define GVSS_STATIC_SLOT_MAX_BYTES (1u << 20)
+cudaError_t launch_search_static_scratch(int metric, int device, const GraphView &g, SearchParams p, uint32_t resident,
+                                         cudaStream_t stream, char *err, size_t err_len);
 // how many single-warp CTAs of the search / build kernel fit the device at this shared-memory size
 uint32_t resident_warps(int device, uint32_t smem_bytes, bool build);
 

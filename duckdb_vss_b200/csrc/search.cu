@@ -131,12 +131,61 @@ uint32_t resident_warps(int device, uint32_t smem_bytes, bool build) {
     return by_smem * (uint32_t)prop.multiProcessorCount;
 }
 
+cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st);
+
 template <int METRIC> static cudaError_t launch_search_t(const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(k_search<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
     if (e != cudaSuccess) return e;
     k_search<METRIC><<<grid, 32, p.sm.bytes, st>>>(g, p);
     count_launch();
     return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Search variant whose scratch memory is a fixed array inside this module instead of a cudaMalloc'ed buffer.
+//
+// Who needs it: callers that must not allocate device memory while they search — a host process that has already
+// handed every free byte of HBM to its own pool (a cudaMalloc from here would fail, or force that pool to give
+// memory back), and callers on a latency-critical path, because cudaMalloc / cudaFree synchronise the whole device
+// and would stall work the caller has queued on other streams.
+//
+// The array is shared by every call on that GPU and keeps whatever the previous call left in it: the kernel clears
+// each visited table before it uses it and the work counter is zeroed on the stream before every launch. Two calls
+// that overlap on the GPU (different streams, or different host threads) would use the same tables at the same
+// time and corrupt each other's results — callers must serialise them.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[GVSS_STATIC_SCRATCH_BYTES];
+
+// The name above is only a host-side handle; the kernel needs the device address, resolved once per device.
+static unsigned char *g_static_scratch_ptr[64];
+
+cudaError_t launch_search_static_scratch(int metric, int device, const GraphView &g, SearchParams p, uint32_t resident,
+                                         cudaStream_t st, char *err, size_t err_len) {
+    if (device < 0 || device >= 64) { snprintf(err, err_len, "device ordinal %d out of range", device); return cudaErrorInvalidDevice; }
+    if (!g_static_scratch_ptr[device]) { // first call on this device (that device is current): do it before any stream capture
+        void *ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+        if (e != cudaSuccess) { snprintf(err, err_len, "cudaGetSymbolAddress(static scratch) failed: %s", cudaGetErrorString(e)); return e; }
+        g_static_scratch_ptr[device] = static_cast<unsigned char *>(ptr);
+    }
+    const size_t header = 256; // work counter
+    const size_t avail = (size_t)GVSS_STATIC_SCRATCH_BYTES - header;
+    if (p.sl.bytes_per_warp > GVSS_STATIC_SLOT_MAX_BYTES) {
+        snprintf(err, err_len,
+                 "gvss_search_device_noalloc: one query slot needs %zu bytes of scratch (beam %u, %u nodes), the built-in "
+                 "scratch array allows %u per slot; use a smaller ef/k or gvss_search_device",
+                 p.sl.bytes_per_warp, p.limit, g.count, (unsigned)GVSS_STATIC_SLOT_MAX_BYTES);
+        return cudaErrorInvalidValue;
+    }
+    uint32_t grid = (uint32_t)(avail / p.sl.bytes_per_warp);
+    if (grid > resident) grid = resident;
+    if (grid > p.nq) grid = (uint32_t)p.nq;
+    p.work_counter = reinterpret_cast<unsigned long long *>(g_static_scratch_ptr[device]);
+    p.scratch = g_static_scratch_ptr[device] + header;
+    cudaError_t e = cudaMemsetAsync(p.work_counter, 0, sizeof(unsigned long long), st);
+    if (e == cudaSuccess) e = launch_search(metric, g, p, grid, st);
+    if (e != cudaSuccess) snprintf(err, err_len, "gvss_search_device_noalloc: launch failed: %s", cudaGetErrorString(e));
+    return e;
 }
 
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {

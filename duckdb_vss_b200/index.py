@@ -88,6 +88,13 @@ class Index:
                                                  C.c_void_p(counts_ptr or None), C.c_void_p(stats_ptr or None),
                                                  C.c_void_p(stream or None)))
 
+    def search_device_noalloc(self, q_ptr, nq, k, ef, keys_ptr, dist_ptr=0, counts_ptr=0, stats_ptr=0, stream=0):
+        """``gvss_search_device_noalloc``: same results as :meth:`search_device`, scratch in the library's built-in array."""
+        capi.check(capi.lib().gvss_search_device_noalloc(self._h, C.c_void_p(q_ptr), int(nq), int(k), int(ef),
+                                                         C.c_void_p(keys_ptr), C.c_void_p(dist_ptr or None),
+                                                         C.c_void_p(counts_ptr or None), C.c_void_p(stats_ptr or None),
+                                                         C.c_void_p(stream or None)))
+
     # --- persistence ---
     def save_to_stream(self, write):
         """``write(bytes) -> bool`` receives the usearch v2.12 stream in pieces (hnsw_index.cpp:526-529)."""

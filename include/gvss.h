@@ -118,6 +118,26 @@ int gvss_search_device(gvss_index *index, const float *queries, uint64_t nq, uin
                        int64_t *keys_out, float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out,
                        void *cuda_stream);
 
+/* Same search as gvss_search_device, for callers that must not allocate device memory while they search. No counterpart
+ * in the reference (usearch allocates freely on the host); it exists for hosts that have given all free HBM to their
+ * own memory pool, where a cudaMalloc from this library would fail or make that pool shrink, and for latency-critical
+ * callers, because cudaMalloc / cudaFree synchronise the whole device. This call runs no cudaMalloc, cudaFree or other
+ * allocating routine: the per-query scratch (visited tables, candidate-queue overflow) lives in a 64 MiB array built
+ * into the library, which every GPU that loads the library holds until the process exits.
+ *  - Limit: one query slot may use at most 1 MiB of the array: 12 bytes per visited-table slot (64*max(ef,k) slots
+ *    rounded up to a power of two, at least 4096) plus one bit per graph node — e.g. ef <= 512 on a 4M-node index,
+ *    ef <= 1024 on 1M nodes. Beyond that the call fails with an error that states the sizes. When fewer slots fit
+ *    than the GPU could run at once, the call is correct but slower than gvss_search_device.
+ *  - Rows staged by gvss_add* must have been inserted with gvss_flush beforehand (flushing allocates; this call
+ *    refuses instead).
+ *  - The first call on each device resolves the array's device address; make that call before any stream capture.
+ *  - All calls on one GPU share the array and it keeps the previous call's contents: the library clears what must
+ *    start clean, but two calls that overlap on the GPU (different streams or threads) race and corrupt each other.
+ *    Serialise them. */
+int gvss_search_device_noalloc(gvss_index *index, const float *queries, uint64_t nq, uint32_t k, uint32_t ef,
+                               int64_t *keys_out, float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out,
+                               void *cuda_stream);
+
 /* --- persistence: usearch v2.12 stream, byte-compatible in both directions ------------ */
 /* index.save_to_stream(cb), hnsw_index.cpp:526-529 (index_dense.hpp:811-878, index.hpp:2709-2749).
  * `write` returns non-zero on success (like the usearch callback returning true). */
