@@ -273,8 +273,8 @@ def main():
 
     # multi-GPU exchange: all-gather of the per-shard lists (12*nq*k bytes per rank) + device merge
     if world > 1:
-        gk = torch.empty((world, nq, k), dtype=torch.int64, device=dev)
-        gd = torch.empty((world, nq, k), dtype=torch.float32, device=dev)
+        gk = torch.empty((world * nq, k), dtype=torch.int64, device=dev)   # rank-major [world][nq][k]
+        gd = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
         mk = torch.empty((nq, k), dtype=torch.int64, device=dev)
         md = torch.empty((nq, k), dtype=torch.float32, device=dev)
 
