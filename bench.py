@@ -188,7 +188,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gvss", choices=["gvss", "reference"])
-    ap.add_argument("--n", type=int, default=1_000_000)
+    ap.add_argument("--vectors", dest="n", type=int, default=1_000_000, help="base vectors per GPU")
     ap.add_argument("--nq", type=int, default=10_000)
     ap.add_argument("--dims", type=int, default=128)
     ap.add_argument("--ef", type=int, default=0, help="0 = smallest ef of the sweep with recall@10 >= 0.95")
