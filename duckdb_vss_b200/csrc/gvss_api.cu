@@ -165,6 +165,17 @@ static int16_t draw_level(uint64_t &state, uint32_t M) {
 
 static int flush_locked(gvss_index *x);
 
+// rows of the staging buffer on the search path: 16 halves the shared memory per query (more resident warps); 32 serves
+// a whole 32-neighbour batch in one go. GVSS_STAGE_ROWS overrides for experiments.
+static uint32_t search_stage_rows() {
+    static uint32_t rows = [] {
+        const char *e = getenv("GVSS_STAGE_ROWS");
+        const uint32_t v = e ? (uint32_t)atoi(e) : 16u;
+        return (v == 32u || v == 16u || v == 8u) ? v : 16u;
+    }();
+    return rows;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // search
 // ------------------------------------------------------------------------------------------------------------
@@ -182,8 +193,8 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     p.trace_query = -1;
     if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
     p.sl = make_scratch_layout(limit, x->count);
-    const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * limit, 256), 2048);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), heap_smem, 0);
+    const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), default_heap_smem(limit), 0, search_stage_rows(), false, list_cap);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
     if (grid > nq) grid = (uint32_t)nq;
@@ -398,8 +409,8 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     p.entry = x->entry; p.max_level = x->max_level < 0 ? 0 : x->max_level;
     p.trace_query = -1;
     p.sl = make_scratch_layout(limit, x->count);
-    const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * limit, 256), 2048);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), heap_smem, 0);
+    const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), default_heap_smem(limit), 0, search_stage_rows(), false, list_cap);
     const uint32_t resident = resident_warps(x->device, p.sm.bytes, false);
     if (!resident) return fail("gvss: no CUDA device");
     char err[384];
@@ -808,8 +819,7 @@ static int flush_locked(gvss_index *x) {
     const uint32_t cmax = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
     p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
-    const uint32_t heap_smem = std::min<uint32_t>(std::max<uint32_t>(4 * p.ef_add, 256), 2048);
-    p.sm = make_smem_layout(x->dpad, top_cap, heap_smem, (2 * cmax + 2) * 8);
+    p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, 32, true, cmax);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
     if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) { cudaFree(d_slots); return 1; }

@@ -51,8 +51,11 @@ struct Cand {
 struct WarpWs {
     float *q;            // dpad floats: the query / the vector being inserted
     float *c;            // 2 × kChunk floats: streamed "left-hand" row chunk for node-to-node distances
-    float *stage[2];     // 2 × 32 rows × rstride floats (second buffer only when dpad > kChunk)
+    float *stage[2];     // 2 × stage_rows × rstride floats (second buffer only when dpad > kChunk)
     uint32_t rstride;    // floats between staged rows (odd multiple of 4 floats -> conflict-free LDS.128)
+    uint32_t stage_rows; // 32 (build: lane <-> candidate) or 16 (search: smaller footprint, more resident warps)
+    uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
+    float *nd;           // ... and their distances
     float *top_d;        // result list, ascending
     uint32_t *top_s;
     Cand *heap;          // candidate queue: first heap_smem entries in shared memory ...
@@ -165,63 +168,77 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
                                                 bool active, uint32_t &staged) {
     const uint32_t lane = lane_id();
     const uint32_t nchunks = (g.dpad + kChunk - 1) / kChunk;
-    const bool single = nchunks == 1;
+    const uint32_t rows = w.stage_rows;
+    const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
-    Acc acc = {0.0f, 0.0f, 0.0f};
+    const uint32_t row = lane & (rows - 1);
+    float result = 0.0f;
 
-    auto issue = [&](uint32_t ch) {
-        const uint32_t buf = ch & 1u;
-        const uint32_t off = ch * kChunk;
-        const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
-        const bool need = active && !(single && staged == my_slot);
-        const uint32_t need_mask = __ballot_sync(kFull, need);
-        const uint32_t ncopy = __popc(need_mask) + (stream_left ? 1u : 0u);
-        if (ncopy == 0) return false;
-#if GVSS_USE_TMA
-        if (lane == 0) mbar_expect_tx(&w.mbar[buf], ncopy * nfl * 4u);
-        __syncwarp();
-        if (need) tma_row(w.stage[buf] + lane * w.rstride, g.vectors + (size_t)my_slot * g.dpad + off, nfl * 4u, &w.mbar[buf]);
-        if (stream_left && lane == 0)
-            tma_row(w.c + buf * kChunk, g.vectors + (size_t)left.slot * g.dpad + off, nfl * 4u, &w.mbar[buf]);
-#else
-        for (uint32_t m = need_mask; m; m &= m - 1) {
-            const uint32_t src = __ffs(m) - 1;
-            const uint32_t s = __shfl_sync(kFull, my_slot, src);
-            if (lane * 4 < nfl) cp_async16(w.stage[buf] + src * w.rstride + lane * 4, g.vectors + (size_t)s * g.dpad + off + lane * 4);
-        }
-        if (stream_left && lane * 4 < nfl)
-            cp_async16(w.c + buf * kChunk + lane * 4, g.vectors + (size_t)left.slot * g.dpad + off + lane * 4);
-        cp_async_commit();
-#endif
-        return true;
-    };
+    // with a 16-row stage the 32 lanes are served in two passes (callers on the search path only use lanes 0..15)
+    for (uint32_t pass = 0; pass * rows < 32; pass++) {
+        const bool act = active && (lane / rows == pass);
+        if (!__ballot_sync(kFull, act)) continue;
+        Acc acc = {0.0f, 0.0f, 0.0f};
 
-    bool pending = issue(0);
-    for (uint32_t ch = 0; ch < nchunks; ch++) {
-        const uint32_t buf = ch & 1u;
-        bool pending_next = false;
-        if (ch + 1 < nchunks) pending_next = issue(ch + 1);
-        if (pending) {
+        auto issue = [&](uint32_t ch) {
+            const uint32_t buf = ch & 1u;
+            const uint32_t off = ch * kChunk;
+            const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
+            const bool need = act && !(cacheable && staged == my_slot);
+            const uint32_t need_mask = __ballot_sync(kFull, need);
+            const uint32_t ncopy = __popc(need_mask) + (stream_left ? 1u : 0u);
+            if (ncopy == 0) return false;
+            float *sbuf = buf ? w.stage[1] : w.stage[0];
 #if GVSS_USE_TMA
-            mbar_wait(&w.mbar[buf], w.phase[buf]);
-            w.phase[buf] ^= 1u;
-#else
-            if (pending_next) cp_async_wait<1>(); else cp_async_wait<0>();
+            uint64_t *bar = w.mbar + buf;
+            if (lane == 0) mbar_expect_tx(bar, ncopy * nfl * 4u);
             __syncwarp();
+            if (need) tma_row(sbuf + row * w.rstride, g.vectors + (size_t)my_slot * g.dpad + off, nfl * 4u, bar);
+            if (stream_left && lane == 0)
+                tma_row(w.c + buf * kChunk, g.vectors + (size_t)left.slot * g.dpad + off, nfl * 4u, bar);
+#else
+            for (uint32_t m = need_mask; m; m &= m - 1) {
+                const uint32_t src = __ffs(m) - 1;
+                const uint32_t s = __shfl_sync(kFull, my_slot, src);
+                if (lane * 4 < nfl) cp_async16(sbuf + (src & (rows - 1)) * w.rstride + lane * 4, g.vectors + (size_t)s * g.dpad + off + lane * 4);
+            }
+            if (stream_left && lane * 4 < nfl)
+                cp_async16(w.c + buf * kChunk + lane * 4, g.vectors + (size_t)left.slot * g.dpad + off + lane * 4);
+            cp_async_commit();
 #endif
+            return true;
+        };
+
+        bool pending = issue(0);
+        for (uint32_t ch = 0; ch < nchunks; ch++) {
+            const uint32_t buf = ch & 1u;
+            bool pending_next = false;
+            if (ch + 1 < nchunks) pending_next = issue(ch + 1);
+            if (pending) {
+#if GVSS_USE_TMA
+                if (buf) { mbar_wait(w.mbar + 1, w.phase[1]); w.phase[1] ^= 1u; }
+                else { mbar_wait(w.mbar, w.phase[0]); w.phase[0] ^= 1u; }
+#else
+                if (pending_next) cp_async_wait<1>(); else cp_async_wait<0>();
+                __syncwarp();
+#endif
+            }
+            const uint32_t off = ch * kChunk;
+            const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
+            if (act) {
+                const float4 *a = reinterpret_cast<const float4 *>(stream_left ? (w.c + buf * kChunk) : (left.smem + off));
+                const float4 *b = reinterpret_cast<const float4 *>((buf ? w.stage[1] : w.stage[0]) + row * w.rstride);
+                acc_chunk<METRIC>(acc, a, b, (int)(nfl / 4));
+            }
+            __syncwarp(); // all lanes are done reading this buffer before it is refilled
+            pending = pending_next;
         }
-        const uint32_t off = ch * kChunk;
-        const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
-        if (active) {
-            const float4 *a = reinterpret_cast<const float4 *>(stream_left ? (w.c + buf * kChunk) : (left.smem + off));
-            const float4 *b = reinterpret_cast<const float4 *>(w.stage[buf] + lane * w.rstride);
-            acc_chunk<METRIC>(acc, a, b, (int)(nfl / 4));
+        if (act) {
+            staged = cacheable ? my_slot : kInvalid;
+            result = acc_finish<METRIC>(acc);
         }
-        __syncwarp(); // all lanes are done reading this buffer before it is refilled
-        pending = pending_next;
     }
-    if (active) staged = single ? my_slot : kInvalid;
-    return acc_finish<METRIC>(acc);
+    return result;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -269,6 +286,42 @@ __device__ __forceinline__ Cand heap_get(const WarpWs &w, uint32_t i) {
 __device__ __forceinline__ void heap_set(WarpWs &w, uint32_t i, Cand v) {
     if (i < w.heap_smem) w.heap[i] = v; else w.heap_ovf[i - w.heap_smem] = v;
 }
+// Drops queue entries that can never be expanded any more (distance above the current radius while the result list is
+// full: the radius only shrinks from there, and such an entry would only end the search when popped). Called when the
+// shared-memory part of the queue is full, instead of letting the queue grow into global memory. The survivors are
+// re-inserted in index order; among entries with EQUAL distance the pop order may then differ from the reference's heap
+// (no effect unless two candidates tie exactly, and never on queues that fit shared memory).
+__device__ __forceinline__ void heap_prune(WarpWs &w, uint32_t &size, float radius) {
+    const uint32_t lane = lane_id();
+    uint32_t kept = 0;
+    for (uint32_t base = 0; base < size; base += 32) {
+        const uint32_t i = base + lane;
+        Cand e = {0.f, 0u};
+        bool keep = false;
+        if (i < size) { e = heap_get(w, i); keep = !(e.d > radius); }
+        const uint32_t km = __ballot_sync(kFull, keep);
+        if (keep) w.heap_ovf[kept + __popc(km & ((1u << lane) - 1u))] = e;
+        kept += __popc(km);
+    }
+    __syncwarp();
+    if (lane == 0) {
+        for (uint32_t j = 0; j < kept; j++) {
+            const Cand e = w.heap_ovf[j];
+            uint32_t i = j;
+            while (i) {
+                const uint32_t p = (i - 1) >> 1;
+                const Cand pe = w.heap[p];
+                if (!(pe.d > e.d)) break;
+                w.heap[i] = pe;
+                i = p;
+            }
+            w.heap[i] = e;
+        }
+    }
+    size = kept;
+    __syncwarp();
+}
+
 __device__ __forceinline__ bool heap_push(WarpWs &w, uint32_t &size, float d, uint32_t s) {
     if (size >= w.heap_total) return false;
     if (lane_id() == 0) {
@@ -396,12 +449,35 @@ __device__ __forceinline__ uint32_t greedy_descent(const GraphView &g, WarpWs &w
     return closest;
 }
 
+// per-lane binary searches over the ascending result list
+__device__ __forceinline__ uint32_t top_lower_bound(const float *td, uint32_t n, float d) { // #{x : x < d}
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (td[mid] < d) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+__device__ __forceinline__ uint32_t top_upper_bound(const float *td, uint32_t n, float d) { // #{x : x <= d}
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (td[mid] <= d) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
 // search_to_find_in_base_ (INSERT=false, index.hpp:3504-3573) / search_to_insert_ (INSERT=true, :3430-3496).
 // On return `top` (w.top_d/top_s, ascending) holds `top_size` results.
+//
+// One expansion handles all unvisited neighbours of the popped node as a batch, with exactly the outcome of the
+// reference's one-by-one loop (`if (top.size() < limit || d < radius) { next.insert; top.insert; radius = top.top() }`):
+//   * radius before candidate j = limit-th smallest of (old top ∪ allowed candidates before j) — a rejected candidate is
+//     never below the radius, so it cannot change that order statistic — hence
+//       accepted_j  <=>  #{x in old top : x <= d_j} + #{i < j allowed : d_i <= d_j} < limit ;
+//   * accepted candidates enter the queue in list order (same heap operations as the reference);
+//   * the new result list is the merge of the old one with the accepted allowed candidates, an element equal to
+//     existing ones going BEFORE them and later candidates before earlier equal ones (sorted_buffer_gt::insert uses
+//     lower_bound), cut at `limit`.
 template <int METRIC, bool INSERT, bool VOLATILE>
 __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, uint32_t limit, int level,
                                             uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged) {
     const uint32_t lane = lane_id();
+    const uint32_t lt_mask = (1u << lane) - 1u;
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
     top_size = 0;
@@ -409,6 +485,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
 
     float radius = warp_distances<METRIC>(g, w, q, start, lane == 0, staged);
     radius = __shfl_sync(kFull, radius, 0);
+    if (radius != radius) radius = CUDART_INF_F;
     cnt.computed++;
     heap_push(w, heap_size, radius, start);
     if (lane == 0) vis_insert(w, start);
@@ -432,40 +509,100 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             printf("pop %u slot %u d %.9g radius %.9g heap %u top %u computed %u\n", cnt.base, c.s, c.d, radius, heap_size, top_size, cnt.computed);
         if (INSERT && c.s == new_slot) continue;
 
+        // 1. unvisited neighbours, compacted in list order (visits.set(): the first occurrence wins)
         uint32_t cap;
         const uint32_t *list = list_ptr(g, c.s, level, cap);
+        uint32_t nnew = 0;
         for (uint32_t base = 0; base < cap; base += 32) {
             const uint32_t idx = base + lane;
             const uint32_t s = idx < cap ? ld_adj<VOLATILE>(list + idx) : kInvalid;
-            const bool valid = s != kInvalid && s < g.count;
             if (!__ballot_sync(kFull, s != kInvalid)) break;
-            // visits.set(): first occurrence wins; duplicates inside one list resolve to the earliest lane
+            const bool valid = s != kInvalid && s < g.count;
             const uint32_t same = __match_any_sync(kFull, s);
             const bool leader = valid && (uint32_t)(__ffs(same) - 1) == lane;
-            bool isnew = false;
             const bool room = w.use_bitmap || nvis < w.vis_limit;
+            bool isnew = false;
             if (leader && room) isnew = vis_insert(w, s);
             const uint32_t nmask = __ballot_sync(kFull, isnew);
             if (!room && __ballot_sync(kFull, leader)) cnt.flags |= 1u;
-            if (!nmask) continue;
+            if (isnew) w.nb[nnew + __popc(nmask & lt_mask)] = s;
+            nnew += __popc(nmask);
             nvis += __popc(nmask);
-            cnt.computed += __popc(nmask);
-            const float d = warp_distances<METRIC>(g, w, q, s, isnew, staged);
+        }
+        __syncwarp();
+        if (!nnew) continue;
+        cnt.computed += nnew;
 
-            // replay the acceptance test in list order; candidates that cannot pass once `top` is full are skipped
-            const bool pre = isnew && (top_size < limit || d < radius);
-            uint32_t cmask = __ballot_sync(kFull, pre);
-            while (cmask) {
-                const uint32_t src = __ffs(cmask) - 1;
-                cmask &= cmask - 1;
-                const float dj = __shfl_sync(kFull, d, src);
-                const uint32_t sj = __shfl_sync(kFull, s, src);
-                if (top_size < limit || dj < radius) {
-                    if (!heap_push(w, heap_size, dj, sj)) cnt.flags |= 1u;
-                    const bool ok = INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX;
-                    if (ok) top_insert(w, top_size, limit, dj, sj);
-                    radius = top_size ? w.top_d[top_size - 1] : CUDART_INF_F;
+        // 2. their distances, stage_rows rows at a time
+        for (uint32_t b = 0; b < nnew; b += w.stage_rows) {
+            const bool act = lane < w.stage_rows && b + lane < nnew;
+            const uint32_t s = act ? w.nb[b + lane] : kInvalid;
+            const float d = warp_distances<METRIC>(g, w, q, s, act, staged);
+            // a NaN distance (NULL / NaN query rows reach the index join, hnsw_lateral_join.test:57-67) is ordered as +inf:
+            // the reference only guarantees termination there, and a total order keeps the merge below well defined
+            if (act) w.nd[b + lane] = (d == d) ? d : CUDART_INF_F;
+        }
+        __syncwarp();
+
+        // 3. acceptance, queue and result-list update, 32 candidates at a time
+        for (uint32_t b = 0; b < nnew; b += 32) {
+            const bool have = b + lane < nnew;
+            const float dj = have ? w.nd[b + lane] : CUDART_INF_F;
+            const uint32_t sj = have ? w.nb[b + lane] : kInvalid;
+            const bool allowed = have && (INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX);
+            const uint32_t amask = __ballot_sync(kFull, allowed);
+            const uint32_t hmask = __ballot_sync(kFull, have);
+            // list size and order statistic as the reference would see them just before candidate j
+            uint32_t le_prev = 0;
+            for (uint32_t m = amask; m; m &= m - 1) {
+                const uint32_t i = __ffs(m) - 1;
+                const float di = __shfl_sync(kFull, dj, i);
+                le_prev += (i < lane && di <= dj) ? 1u : 0u;
+            }
+            const uint32_t size_before = top_size + __popc(amask & lt_mask);
+            const uint32_t le_top = have ? top_upper_bound(w.top_d, top_size, dj) : 0u;
+            const bool acc = have && (size_before < limit || le_top + le_prev < limit);
+            const uint32_t accmask = __ballot_sync(kFull, acc);
+            (void)hmask;
+            if (!accmask) continue;
+
+            for (uint32_t m = accmask; m; m &= m - 1) { // next.insert in list order
+                const uint32_t i = __ffs(m) - 1;
+                if (heap_size == w.heap_smem && top_size == limit) heap_prune(w, heap_size, radius);
+                if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
+            }
+
+            const bool ins = acc && allowed;
+            const uint32_t imask = __ballot_sync(kFull, ins);
+            const uint32_t m_ins = __popc(imask);
+            if (m_ins) {
+                const uint32_t lb = ins ? top_lower_bound(w.top_d, top_size, dj) : 0xFFFFFFFFu;
+                uint32_t before = 0; // inserted candidates that end up in front of this one
+                for (uint32_t m = imask; m; m &= m - 1) {
+                    const uint32_t i = __ffs(m) - 1;
+                    const float di = __shfl_sync(kFull, dj, i);
+                    before += (di < dj || (di == dj && i > lane)) ? 1u : 0u;
                 }
+                const uint32_t pmin = __reduce_min_sync(kFull, lb);
+                // old elements [pmin, top_size) move up by the number of insertions at or before them; windows from the top
+                for (int32_t hi = (int32_t)top_size; hi > (int32_t)pmin; hi -= 32) {
+                    const int32_t i = hi - 1 - (int32_t)lane;
+                    const bool mv = i >= (int32_t)pmin;
+                    float td = 0.f;
+                    uint32_t ts = 0, sh = 0;
+                    if (mv) { td = w.top_d[i]; ts = w.top_s[i]; }
+                    for (uint32_t m = imask; m; m &= m - 1) {
+                        const uint32_t pa = __shfl_sync(kFull, lb, __ffs(m) - 1);
+                        sh += ((int32_t)pa <= i) ? 1u : 0u;
+                    }
+                    __syncwarp();
+                    if (mv && (uint32_t)i + sh < limit) { w.top_d[i + sh] = td; w.top_s[i + sh] = ts; }
+                    __syncwarp();
+                }
+                if (ins && lb + before < limit) { w.top_d[lb + before] = dj; w.top_s[lb + before] = sj; }
+                top_size = min(limit, top_size + m_ins);
+                __syncwarp();
+                radius = w.top_d[top_size - 1];
             }
         }
     }

@@ -17,6 +17,9 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
     w.top_d = reinterpret_cast<float *>(smem + sm.off_top_d);
     w.top_s = reinterpret_cast<uint32_t *>(smem + sm.off_top_s);
     w.rstride = sm.rstride;
+    w.stage_rows = sm.stage_rows;
+    w.nb = reinterpret_cast<uint32_t *>(smem + sm.off_nb);
+    w.nd = reinterpret_cast<float *>(smem + sm.off_nd);
     w.heap_smem = sm.heap_smem;
     uint8_t *base = scratch + (size_t)blockIdx.x * sl.bytes_per_warp;
     w.vis = reinterpret_cast<uint32_t *>(base);
@@ -81,27 +84,40 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
     }
 }
 
-SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes) {
+SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
+                            bool with_left, uint32_t list_cap) {
     SmemLayout s{};
     const uint32_t chunkf = dpad < (uint32_t)kChunk ? dpad : (uint32_t)kChunk;
     s.rstride = chunkf + (((chunkf / 4) % 2 == 0) ? 4u : 0u); // odd number of 16-byte granules per row
-    const uint32_t stage_bytes = 32u * s.rstride * 4u;
+    s.stage_rows = stage_rows;
+    const uint32_t stage_bytes = stage_rows * s.rstride * 4u;
     const bool two = dpad > (uint32_t)kChunk;
     uint32_t off = 0;
     auto take = [&](uint32_t bytes, uint32_t align) { off = (off + align - 1) / align * align; uint32_t o = off; off += bytes; return o; };
     s.off_mbar = take(16, 16);
     s.off_stage0 = take(stage_bytes, 128);
     s.off_stage1 = two ? take(stage_bytes, 128) : s.off_stage0;
-    s.off_c = take(2 * kChunk * 4, 128);
+    s.off_c = take(with_left ? 2 * kChunk * 4 : 0, 128);
     s.off_q = take(dpad * 4, 16);
     s.heap_smem = heap_smem;
     s.off_heap = take(heap_smem * 8, 16);
     s.top_cap = top_cap;
     s.off_top_d = take(top_cap * 4, 16);
     s.off_top_s = take(top_cap * 4, 16);
+    const uint32_t lc = (list_cap + 31) / 32 * 32;
+    s.off_nb = take(lc * 4, 16);
+    s.off_nd = take(lc * 4, 16);
     s.off_misc = take(misc_bytes, 16);
     s.bytes = (off + 127) / 128 * 128;
     return s;
+}
+
+// Queue entries kept in shared memory. Live entries (distance <= radius) are at most beam + ties, so beam + 25 % head-room
+// (at least 256) is enough once dead entries are pruned when it fills up (heap_prune).
+uint32_t default_heap_smem(uint32_t beam) {
+    uint32_t h = beam + (beam / 4 > 128 ? beam / 4 : 128);
+    if (h < 256) h = 256;
+    return (h + 31) / 32 * 32;
 }
 
 ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes) {
@@ -121,14 +137,22 @@ ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes) {
 }
 
 uint32_t resident_warps(int device, uint32_t smem_bytes, bool build) {
-    cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0;
-    size_t per_sm = prop.sharedMemPerMultiprocessor;
-    uint32_t by_smem = (uint32_t)(per_sm / (smem_bytes + 1024)); // 1 KB is reserved per CTA
-    uint32_t cap = build ? 16u : 32u; // build warps hold more registers/scratch; 32 = CTA-per-SM limit
+    // cudaGetDeviceProperties costs milliseconds: ask once per device
+    static size_t smem_per_sm[64];
+    static int sm_count[64];
+    if (device < 0 || device >= 64) return 0;
+    if (!sm_count[device]) {
+        int sms = 0, smem = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return 0;
+        if (cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device) != cudaSuccess) return 0;
+        smem_per_sm[device] = (size_t)smem;
+        sm_count[device] = sms;
+    }
+    uint32_t by_smem = (uint32_t)(smem_per_sm[device] / (smem_bytes + 1024)); // 1 KB is reserved per CTA
+    const uint32_t cap = build ? 16u : 32u; // 32 = CTA-per-SM limit; build warps also hold a node lock at times
     if (by_smem > cap) by_smem = cap;
     if (by_smem < 1) by_smem = 1;
-    return by_smem * (uint32_t)prop.multiProcessorCount;
+    return by_smem * (uint32_t)sm_count[device];
 }
 
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st);
