@@ -258,20 +258,69 @@ __device__ __forceinline__ void vis_clear(WarpWs &w) {
     }
     __syncwarp();
 }
-// returns true when `key` was not yet present (and is now)
+constexpr uint32_t kVisWindow = 8; // slots per probe window = one 32-byte sector
+
+// returns true when `key` was not yet present (and is now). Single-lane form (atomicCAS over the probe windows).
 __device__ __forceinline__ bool vis_insert(WarpWs &w, uint32_t key) {
     if (w.use_bitmap) {
         const uint32_t bit = 1u << (key & 31u);
         return (atomicOr(&w.bitmap[key >> 5], bit) & bit) == 0u;
     }
-    uint32_t h = (key * 2654435761u) >> 7;
+    uint32_t h = ((key * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1);
     for (;;) {
-        h &= w.vis_mask;
-        const uint32_t old = atomicCAS(&w.vis[h], kInvalid, key);
-        if (old == kInvalid) return true;
-        if (old == key) return false;
-        h++;
+        for (uint32_t j = 0; j < kVisWindow; j++) {
+            const uint32_t old = atomicCAS(&w.vis[h + j], kInvalid, key);
+            if (old == kInvalid) return true;
+            if (old == key) return false;
+        }
+        h = (h + kVisWindow) & w.vis_mask;
     }
+}
+
+// Warp-wide form: every lane with `want` tests-and-sets its own key; keys of wanting lanes are distinct.
+// The table belongs to this warp alone, so no atomics are needed: each lane reads its 8-slot window (one 32-byte
+// sector, one L2 round trip), lanes that target the same empty slot are ordered by lane id in registers
+// (__match_any_sync), winners write with a plain store; a lane whose window is full — or was filled by the winners —
+// moves to the next window of its probe sequence. A key lives in the first window of its sequence that had room when
+// it was inserted, so a lookup ends at the first window with an empty slot.
+__device__ __forceinline__ bool vis_insert_warp(WarpWs &w, uint32_t key, bool want) {
+    if (w.use_bitmap) return want ? vis_insert(w, key) : false;
+    const uint32_t lane = lane_id();
+    uint32_t base = ((key * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1);
+    bool pending = want, isnew = false;
+    while (__ballot_sync(kFull, pending)) {
+        uint4 a = make_uint4(0u, 0u, 0u, 0u), b = a;
+        if (pending) {
+            a = __ldcg(reinterpret_cast<const uint4 *>(w.vis + base));
+            b = __ldcg(reinterpret_cast<const uint4 *>(w.vis + base + 4));
+        }
+        const uint32_t e[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        bool found = false;
+        uint32_t empties = 0; // bit j: slot j of the window is empty
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            found |= e[j] == key;
+            empties |= (e[j] == kInvalid) ? (1u << j) : 0u;
+        }
+        if (pending && found) pending = false;
+        bool claiming = pending && empties != 0u;
+        for (;;) { // settle contested slots: the lowest lane keeps it, the others move to their next empty slot
+            const uint32_t pos = claiming ? base + (uint32_t)(__ffs(empties) - 1) : (0x80000000u | lane);
+            const uint32_t peers = __match_any_sync(kFull, pos);
+            const bool lost = claiming && (uint32_t)(__ffs(peers) - 1) != lane;
+            if (!__ballot_sync(kFull, lost)) {
+                if (claiming) { __stcg(w.vis + pos, key); isnew = true; pending = false; }
+                break;
+            }
+            if (lost) {
+                empties &= empties - 1;
+                if (!empties) claiming = false; // every empty slot went to a lower lane: window is full now
+            }
+        }
+        __syncwarp();
+        if (pending) base = (base + kVisWindow) & w.vis_mask;
+    }
+    return isnew;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -521,8 +570,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const uint32_t same = __match_any_sync(kFull, s);
             const bool leader = valid && (uint32_t)(__ffs(same) - 1) == lane;
             const bool room = w.use_bitmap || nvis < w.vis_limit;
-            bool isnew = false;
-            if (leader && room) isnew = vis_insert(w, s);
+            const bool isnew = vis_insert_warp(w, s, leader && room);
             const uint32_t nmask = __ballot_sync(kFull, isnew);
             if (!room && __ballot_sync(kFull, leader)) cnt.flags |= 1u;
             if (isnew) w.nb[nnew + __popc(nmask & lt_mask)] = s;

@@ -3,6 +3,7 @@
 // (:3504-3573) as called by index_dense_gt::search_ (index_dense.hpp:1797-1827) from HNSWIndex::InitializeScan /
 // ExecuteMultiScan (hnsw_index.cpp:285-311, 353-367).
 #include "kernels.h"
+#include <cstdlib>
 
 namespace gvss {
 
@@ -124,7 +125,8 @@ ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes) {
     // visited members per search ~ 20*beam + 500 on the measured data sets; 64*beam slots
     // (min 4096) keep the table under ~40 % load, the kernel flags a query that would exceed 75 %.
     ScratchLayout s{};
-    uint32_t want = beam * 64u;
+    static const uint32_t factor = [] { const char *e = getenv("GVSS_VIS_FACTOR"); const uint32_t v = e ? (uint32_t)atoi(e) : 64u; return v ? v : 64u; }();
+    uint32_t want = beam * factor;
     if (want < 4096u) want = 4096u;
     uint32_t v = 4096u;
     while (v < want) v <<= 1;
