@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgvss.so")
+LIB_PATH = os.environ.get("GVSS_LIB") or os.path.join(HERE, "libgvss.so")  # GVSS_LIB: A/B builds of the same library
 
 
 class GvssError(RuntimeError):

@@ -108,6 +108,7 @@ __device__ __forceinline__ void tma_row(void *dst, const void *src, uint32_t byt
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
@@ -557,6 +558,11 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         if ((cnt.flags & 0x80000000u) && lane == 0)
             printf("pop %u slot %u d %.9g radius %.9g heap %u top %u computed %u\n", cnt.base, c.s, c.d, radius, heap_size, top_size, cnt.computed);
         if (INSERT && c.s == new_slot) continue;
+        if (heap_size) { // the next candidate is most likely the current queue head: pull its adjacency row towards L2
+            uint32_t pcap;
+            const uint32_t *plist = list_ptr(g, heap_get(w, 0).s, level, pcap);
+            if (lane * 32 < pcap) prefetch_l2(plist + lane * 32);
+        }
 
         // 1. unvisited neighbours, compacted in list order (visits.set(): the first occurrence wins)
         uint32_t cap;
@@ -581,7 +587,11 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         if (!nnew) continue;
         cnt.computed += nnew;
 
-        // 2. their distances, stage_rows rows at a time
+        // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
+        for (uint32_t i = w.stage_rows * 4 + lane; i < nnew * 4; i += 32) {
+            const uint32_t lines = (g.dpad * 4 + 127) / 128;
+            if ((i & 3u) < lines) prefetch_l2(g.vectors + (size_t)w.nb[i >> 2] * g.dpad + (i & 3u) * 32);
+        }
         for (uint32_t b = 0; b < nnew; b += w.stage_rows) {
             const bool act = lane < w.stage_rows && b + lane < nnew;
             const uint32_t s = act ? w.nb[b + lane] : kInvalid;
@@ -597,9 +607,12 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const bool have = b + lane < nnew;
             const float dj = have ? w.nd[b + lane] : CUDART_INF_F;
             const uint32_t sj = have ? w.nb[b + lane] : kInvalid;
-            const bool allowed = have && (INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX);
+            // once the result list is full a candidate at or above the radius can neither be accepted nor influence the
+            // acceptance of a later one (the radius only shrinks), so the group is thinned before any bookkeeping
+            const bool maybe = have && (top_size < limit || dj < radius);
+            if (!__ballot_sync(kFull, maybe)) continue;
+            const bool allowed = maybe && (INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX);
             const uint32_t amask = __ballot_sync(kFull, allowed);
-            const uint32_t hmask = __ballot_sync(kFull, have);
             // list size and order statistic as the reference would see them just before candidate j
             uint32_t le_prev = 0;
             for (uint32_t m = amask; m; m &= m - 1) {
@@ -608,10 +621,9 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                 le_prev += (i < lane && di <= dj) ? 1u : 0u;
             }
             const uint32_t size_before = top_size + __popc(amask & lt_mask);
-            const uint32_t le_top = have ? top_upper_bound(w.top_d, top_size, dj) : 0u;
-            const bool acc = have && (size_before < limit || le_top + le_prev < limit);
+            const uint32_t le_top = maybe ? top_upper_bound(w.top_d, top_size, dj) : 0u;
+            const bool acc = maybe && (size_before < limit || le_top + le_prev < limit);
             const uint32_t accmask = __ballot_sync(kFull, acc);
-            (void)hmask;
             if (!accmask) continue;
 
             for (uint32_t m = accmask; m; m &= m - 1) { // next.insert in list order
