@@ -14,7 +14,9 @@
 namespace gvss {
 
 __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
-                                            const ScratchLayout &sl) {
+                                            const ScratchLayout &sl, int direct) {
+    w.direct = (direct & 1) != 0;
+    w.spec_prefetch = (direct & 2) != 0;
     w.mbar = reinterpret_cast<uint64_t *>(smem + sm.off_mbar);
     w.stage[0] = reinterpret_cast<float *>(smem + sm.off_stage0);
     w.stage[1] = reinterpret_cast<float *>(smem + sm.off_stage1);
@@ -106,7 +108,7 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
 template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     WarpWs w;
-    carve_build(w, smem, p.sm, p.scratch, p.sl);
+    carve_build(w, smem, p.sm, p.scratch, p.sl, p.direct);
     const uint32_t lane = lane_id();
     const uint32_t cmax = max(g.M, g.M0);
     uint32_t *mine_s = reinterpret_cast<uint32_t *>(smem + p.sm.off_misc);

@@ -165,6 +165,11 @@ static int16_t draw_level(uint64_t &state, uint32_t M) {
 
 static int flush_locked(gvss_index *x);
 
+// heap entries held in shared memory on the search path (GVSS_HEAP_SMEM overrides default_heap_smem for experiments)
+static uint32_t search_heap_smem(uint32_t limit) {
+    static int v = [] { const char *e = getenv("GVSS_HEAP_SMEM"); return e ? atoi(e) : 0; }();
+    return v > 0 ? (uint32_t)v : default_heap_smem(limit);
+}
 // rows of the staging buffer on the search path: 16 halves the shared memory per query (more resident warps); 32 serves
 // a whole 32-neighbour batch in one go. GVSS_STAGE_ROWS overrides for experiments.
 static uint32_t search_stage_rows() {
@@ -174,6 +179,17 @@ static uint32_t search_stage_rows() {
         return (v == 32u || v == 16u || v == 8u) ? v : 16u;
     }();
     return rows;
+}
+// query-to-node distances: 0 = rows staged in shared memory by TMA bulk copies (default: faster once the base set
+// exceeds L2, profiles/r1_search_ncu_summary.txt), 1 = rows streamed straight into registers (256-bit loads, no staging). GVSS_DIRECT_ROWS overrides for A/B measurements.
+static bool direct_rows() {
+    static bool on = [] { const char *e = getenv("GVSS_DIRECT_ROWS"); return GVSS_DIRECT_PATH && e ? atoi(e) != 0 : false; }();
+    return on;
+}
+// prefetch every listed neighbour's row to L2 before the visited test resolves (GVSS_SPEC_PREFETCH=0/1)
+static bool spec_prefetch() {
+    static bool on = [] { const char *e = getenv("GVSS_SPEC_PREFETCH"); return e ? atoi(e) != 0 : false; }();
+    return on;
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -194,7 +210,8 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), default_heap_smem(limit), 0, search_stage_rows(), false, list_cap);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap);
+    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
     if (grid > nq) grid = (uint32_t)nq;
@@ -238,7 +255,7 @@ int gvss_create(const gvss_config *config, gvss_index **out) {
     if (x->cfg.device < 0) cudaGetDevice(&x->device); else x->device = x->cfg.device;
     if (x->device >= ndev) { delete x; return fail("gvss_create: device %d out of range", x->device); }
     cudaSetDevice(x->device);
-    x->dpad = (x->cfg.dimensions + 3) / 4 * 4;
+    x->dpad = (x->cfg.dimensions + 7) / 8 * 8; // 32-byte rows: TMA bulk copies need 16 B, the 256-bit row loads 32 B
     x->stride0 = (x->cfg.connectivity_base + 7) / 8 * 8;
     x->strideU = (x->cfg.connectivity + 7) / 8 * 8;
     if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -410,7 +427,8 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     p.trace_query = -1;
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), default_heap_smem(limit), 0, search_stage_rows(), false, list_cap);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap);
+    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
     const uint32_t resident = resident_warps(x->device, p.sm.bytes, false);
     if (!resident) return fail("gvss: no CUDA device");
     char err[384];
@@ -820,6 +838,7 @@ static int flush_locked(gvss_index *x) {
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
     p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
     p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, 32, true, cmax);
+    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
     if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) { cudaFree(d_slots); return 1; }

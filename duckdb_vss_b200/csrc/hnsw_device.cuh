@@ -20,6 +20,12 @@
 #ifndef GVSS_USE_TMA
 #define GVSS_USE_TMA 1
 #endif
+// Alternative row path kept for A/B measurements only (build with -DGVSS_DIRECT_PATH=1, run with GVSS_DIRECT_ROWS=1):
+// every lane streams its own row into registers with 256-bit loads, no shared-memory staging. It costs 128 registers per
+// thread and lost to TMA staging once the base set exceeds L2 (profiles/r1_search_ncu_summary.txt).
+#ifndef GVSS_DIRECT_PATH
+#define GVSS_DIRECT_PATH 0
+#endif
 
 namespace gvss {
 
@@ -54,6 +60,8 @@ struct WarpWs {
     float *stage[2];     // 2 × stage_rows × rstride floats (second buffer only when dpad > kChunk)
     uint32_t rstride;    // floats between staged rows (odd multiple of 4 floats -> conflict-free LDS.128)
     uint32_t stage_rows; // 32 (build: lane <-> candidate) or 16 (search: smaller footprint, more resident warps)
+    bool spec_prefetch;  // prefetch every neighbour's row to L2 before the visited test resolves (trades HBM traffic for latency)
+    bool direct;         // query-to-node distances stream each lane's row straight into registers (no staging)
     uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
     float *nd;           // ... and their distances
     float *top_d;        // result list, ascending
@@ -136,14 +144,13 @@ template <int METRIC> __device__ __forceinline__ void acc_step(Acc &r, float a, 
         r.b2 = __fadd_rn(r.b2, __fmul_rn(b, b));
     }
 }
+template <int METRIC> __device__ __forceinline__ void acc_pair(Acc &r, float2 a, float2 b);
 template <int METRIC> __device__ __forceinline__ void acc_chunk(Acc &r, const float4 *a, const float4 *b, int n4) {
 #pragma unroll 4
     for (int i = 0; i < n4; i++) {
-        float4 x = a[i], y = b[i];
-        acc_step<METRIC>(r, x.x, y.x);
-        acc_step<METRIC>(r, x.y, y.y);
-        acc_step<METRIC>(r, x.z, y.z);
-        acc_step<METRIC>(r, x.w, y.w);
+        const float4 x = a[i], y = b[i];
+        acc_pair<METRIC>(r, make_float2(x.x, x.y), make_float2(y.x, y.y));
+        acc_pair<METRIC>(r, make_float2(x.z, x.w), make_float2(y.z, y.w));
     }
 }
 template <int METRIC> __device__ __forceinline__ float acc_finish(const Acc &r) {
@@ -153,6 +160,69 @@ template <int METRIC> __device__ __forceinline__ float acc_finish(const Acc &r) 
     if (r.a2 == 0.0f && r.b2 == 0.0f) return 0.0f;
     if (r.a2 == 0.0f || r.b2 == 0.0f) return 1.0f;
     return __fsub_rn(1.0f, __fdiv_rn(r.ab, __fmul_rn(__fsqrt_rn(r.a2), __fsqrt_rn(r.b2))));
+}
+
+// ---- register-streamed rows: each lane reads ITS row with 256-bit loads (one 32-byte sector per load, SASS LDG.E.ENL2.256)
+// and folds it against the query held in shared memory. Differences and products of two neighbouring dimensions are
+// formed with packed FP32x2 instructions (FADD2 / FMUL2, round-to-nearest per element), the sum itself stays one strict
+// left-to-right chain — so the bits are the same as in acc_step.
+__device__ __forceinline__ void ldg256(const float *p, float (&v)[8]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ float2 sub2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)));
+    return *reinterpret_cast<float2 *>(&r);
+}
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) {
+    unsigned long long r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)));
+    return *reinterpret_cast<float2 *>(&r);
+}
+template <int METRIC> __device__ __forceinline__ void acc_pair(Acc &r, float2 a, float2 b) {
+    if (METRIC == kL2sq) {
+        const float2 t = sub2(a, b);
+        const float2 p = mul2(t, t);
+        r.ab = __fadd_rn(__fadd_rn(r.ab, p.x), p.y);
+    } else {
+        const float2 p = mul2(a, b);
+        r.ab = __fadd_rn(__fadd_rn(r.ab, p.x), p.y);
+        if (METRIC == kCos) {
+            const float2 pa = mul2(a, a), pb = mul2(b, b);
+            r.a2 = __fadd_rn(__fadd_rn(r.a2, pa.x), pa.y);
+            r.b2 = __fadd_rn(__fadd_rn(r.b2, pb.x), pb.y);
+        }
+    }
+}
+// d(query in shared memory, row `my_slot`) for every active lane; dpad is a multiple of 8 floats
+template <int METRIC>
+__device__ __noinline__ float direct_distance(const float *vectors, uint32_t dpad, const float *qs, uint32_t my_slot, bool active) {
+    Acc acc = {0.0f, 0.0f, 0.0f};
+    if (active) {
+        const float *row = vectors + (size_t)my_slot * dpad;
+        const uint32_t n8 = dpad / 8;
+#pragma unroll 1
+        for (uint32_t base = 0; base < n8; base += 4) { // 4 sectors (one 128-byte line) in flight per lane
+            float v[4][8];
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (base + j < n8) ldg256(row + (base + j) * 8, v[j]);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if (base + j < n8) {
+                    const float4 q0 = *reinterpret_cast<const float4 *>(qs + (base + j) * 8);
+                    const float4 q1 = *reinterpret_cast<const float4 *>(qs + (base + j) * 8 + 4);
+                    acc_pair<METRIC>(acc, make_float2(q0.x, q0.y), make_float2(v[j][0], v[j][1]));
+                    acc_pair<METRIC>(acc, make_float2(q0.z, q0.w), make_float2(v[j][2], v[j][3]));
+                    acc_pair<METRIC>(acc, make_float2(q1.x, q1.y), make_float2(v[j][4], v[j][5]));
+                    acc_pair<METRIC>(acc, make_float2(q1.z, q1.w), make_float2(v[j][6], v[j][7]));
+                }
+            }
+        }
+    }
+    return acc_finish<METRIC>(acc);
 }
 
 // Where the left-hand vector of a distance batch comes from.
@@ -172,6 +242,13 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
+#if GVSS_DIRECT_PATH
+    if (w.direct && !stream_left) { // no staging at all: all 32 lanes at once
+        const float d = direct_distance<METRIC>(g.vectors, g.dpad, left.smem, my_slot, active);
+        __syncwarp();
+        return d;
+    }
+#endif
     const uint32_t row = lane & (rows - 1);
     float result = 0.0f;
 
@@ -573,6 +650,10 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const uint32_t s = idx < cap ? ld_adj<VOLATILE>(list + idx) : kInvalid;
             if (!__ballot_sync(kFull, s != kInvalid)) break;
             const bool valid = s != kInvalid && s < g.count;
+            if (w.spec_prefetch && valid) { // start pulling the row towards L2 while the visited test is in flight
+                const float *row = g.vectors + (size_t)s * g.dpad;
+                for (uint32_t l = 0; l * 32 < g.dpad; l++) prefetch_l2(row + l * 32);
+            }
             const uint32_t same = __match_any_sync(kFull, s);
             const bool leader = valid && (uint32_t)(__ffs(same) - 1) == lane;
             const bool room = w.use_bitmap || nvis < w.vis_limit;
@@ -588,12 +669,13 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         cnt.computed += nnew;
 
         // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
-        for (uint32_t i = w.stage_rows * 4 + lane; i < nnew * 4; i += 32) {
+        const uint32_t bw = (GVSS_DIRECT_PATH && w.direct) ? 32u : w.stage_rows; // rows per distance batch
+        for (uint32_t i = bw * 4 + lane; i < nnew * 4; i += 32) {
             const uint32_t lines = (g.dpad * 4 + 127) / 128;
             if ((i & 3u) < lines) prefetch_l2(g.vectors + (size_t)w.nb[i >> 2] * g.dpad + (i & 3u) * 32);
         }
-        for (uint32_t b = 0; b < nnew; b += w.stage_rows) {
-            const bool act = lane < w.stage_rows && b + lane < nnew;
+        for (uint32_t b = 0; b < nnew; b += bw) {
+            const bool act = lane < bw && b + lane < nnew;
             const uint32_t s = act ? w.nb[b + lane] : kInvalid;
             const float d = warp_distances<METRIC>(g, w, q, s, act, staged);
             // a NaN distance (NULL / NaN query rows reach the index join, hnsw_lateral_join.test:57-67) is ordered as +inf:

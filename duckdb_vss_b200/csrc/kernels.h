@@ -40,6 +40,7 @@ struct SearchParams {
     ScratchLayout sl;
     SmemLayout sm;
     long long trace_query; // -1 = off
+    int direct;            // bit0: stream rows into registers instead of staging them; bit1: speculative row prefetch
 };
 // grid = number of resident warps; returns cudaError
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);
@@ -60,6 +61,7 @@ struct BuildParams {
     unsigned long long *work_counter;
     uint32_t *locks;         // [capacity] per-node spin locks (index.hpp:3214-3224 nodes_mutexes_)
     uint32_t ef_add;
+    int direct;
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;

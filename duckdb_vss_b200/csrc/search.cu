@@ -8,7 +8,9 @@
 namespace gvss {
 
 __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
-                                      const ScratchLayout &sl) {
+                                      const ScratchLayout &sl, int direct) {
+    w.direct = (direct & 1) != 0;
+    w.spec_prefetch = (direct & 2) != 0;
     w.mbar = reinterpret_cast<uint64_t *>(smem + sm.off_mbar);
     w.stage[0] = reinterpret_cast<float *>(smem + sm.off_stage0);
     w.stage[1] = reinterpret_cast<float *>(smem + sm.off_stage1);
@@ -18,7 +20,7 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
     w.top_d = reinterpret_cast<float *>(smem + sm.off_top_d);
     w.top_s = reinterpret_cast<uint32_t *>(smem + sm.off_top_s);
     w.rstride = sm.rstride;
-    w.stage_rows = sm.stage_rows;
+    w.stage_rows = sm.stage_rows ? sm.stage_rows : 32u;
     w.nb = reinterpret_cast<uint32_t *>(smem + sm.off_nb);
     w.nd = reinterpret_cast<float *>(smem + sm.off_nd);
     w.heap_smem = sm.heap_smem;
@@ -43,7 +45,7 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
 template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g, SearchParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     WarpWs w;
-    carve(w, smem, p.sm, p.scratch, p.sl);
+    carve(w, smem, p.sm, p.scratch, p.sl, p.direct);
     const uint32_t lane = lane_id();
     uint32_t staged = kInvalid;
 
@@ -113,10 +115,11 @@ SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem,
     return s;
 }
 
-// Queue entries kept in shared memory. Live entries (distance <= radius) are at most beam + ties, so beam + 25 % head-room
-// (at least 256) is enough once dead entries are pruned when it fills up (heap_prune).
+// Queue entries kept in shared memory. Live entries (distance <= radius) are the not-yet-expanded part of the result
+// list plus ties, in practice well under half the beam, so beam/2 + 64 (at least 256) is enough once dead entries are
+// pruned when it fills up (heap_prune); measured best among 128/256/512 at beam 384 (profiles/r1_search_ncu_summary.txt).
 uint32_t default_heap_smem(uint32_t beam) {
-    uint32_t h = beam + (beam / 4 > 128 ? beam / 4 : 128);
+    uint32_t h = beam / 2 + 64;
     if (h < 256) h = 256;
     return (h + 31) / 32 * 32;
 }
