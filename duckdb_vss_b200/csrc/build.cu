@@ -96,7 +96,11 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
             if (nkept == needed) break;
             const bool act = alive && lane > j;
             if (__ballot_sync(kFull, act)) {
-                const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, sj}, cs, act, staged);
+                // the kept candidate's own row usually sits in the stage already (row j, single-chunk rows): then the
+                // step needs no memory access at all
+                const bool resident = g.dpad <= (uint32_t)kChunk && w.stage_rows == 32 && __shfl_sync(kFull, staged, j) == sj;
+                const LeftSrc left = resident ? LeftSrc{w.stage[0] + j * w.rstride, 0} : LeftSrc{nullptr, sj};
+                const float d = warp_distances<METRIC>(g, w, left, cs, act, staged);
                 if (act && d < cd) alive = false;
             }
             amask = __ballot_sync(kFull, alive && lane > j);
@@ -143,10 +147,13 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         const uint32_t entry = (uint32_t)(es & 0xFFFFFFFFull);
 
         Counters cnt = {0, 0, 0, 0};
+        long long t0 = clock64(), t_beam = 0, t_refine = 0, t_conn = 0, t_recon = 0;
         uint32_t closest = greedy_descent<METRIC, true>(g, w, entry, max_level, level, cnt, staged);
+        const long long t_greedy = clock64() - t0;
 
         for (int l = min(level, max_level); l >= 0; --l) {
             uint32_t top_size = 0;
+            t0 = clock64();
             beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
             if (cnt.flags & 1u) { // visited table would have overfilled: redo the level with the exact bitmap
                 cnt.flags = 0;
@@ -157,8 +164,10 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
 
             // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)
             const uint32_t cap_l = l ? g.M : g.M0;
+            t_beam += clock64() - t0; t0 = clock64();
             uint32_t nk = refine<METRIC>(g, w, top_size, g.M, kept_s, kept_d, staged);
             nk = min(nk, cap_l);
+            t_refine += clock64() - t0; t0 = clock64();
             for (uint32_t i = lane; i < nk; i += 32) mine_s[i] = kept_s[i];
             __syncwarp();
             uint32_t capx;
@@ -179,6 +188,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             }
             unlock_node(p.locks, slot);
             closest = mine_s[0];
+            t_conn += clock64() - t0; t0 = clock64();
 
             // reconnect_neighbor_nodes_
             for (uint32_t i = 0; i < nk; i++) {
@@ -220,8 +230,13 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                 for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
                 unlock_node(p.locks, close);
             }
+            t_recon += clock64() - t0;
         }
-
+        if (p.prof && lane == 0) {
+            atomicAdd(p.prof + 0, (unsigned long long)t_greedy); atomicAdd(p.prof + 1, (unsigned long long)t_beam);
+            atomicAdd(p.prof + 2, (unsigned long long)t_refine); atomicAdd(p.prof + 3, (unsigned long long)t_conn);
+            atomicAdd(p.prof + 4, (unsigned long long)t_recon); atomicAdd(p.prof + 5, 1ull);
+        }
         // a node above the current top level becomes the entry point once it is connected: index.hpp:2372-2376
         if (level > max_level && lane == 0) {
             const unsigned long long mineEs = ((unsigned long long)(uint32_t)level << 32) | slot;

@@ -122,16 +122,26 @@ __global__ void __launch_bounds__(kRows) k_exact(const float *__restrict__ base,
             const uint32_t nf4 = min((uint32_t)kDimChunk, dpad - ch * kDimChunk) / 4;
             for (uint32_t c4 = 0; c4 < nf4; c4++) {
                 const float4 x = brow[c4];
+                const float2 x01 = make_float2(x.x, x.y), x23 = make_float2(x.z, x.w);
+                // differences / products of two neighbouring dimensions with packed FP32x2 (FADD2 / FMUL2, RN per element);
+                // the sums stay strict left-to-right chains
+                float2 xx01 = x01, xx23 = x23;
+                if (METRIC == 'c') { xx01 = mul2(x01, x01); xx23 = mul2(x23, x23); }
 #pragma unroll
                 for (int j = 0; j < QT; j++) {
                     const float4 y = *reinterpret_cast<const float4 *>(sq + j * dpad + ch * kDimChunk + c4 * 4);
-                    const float xs[4] = {x.x, x.y, x.z, x.w}, ys[4] = {y.x, y.y, y.z, y.w};
-#pragma unroll
-                    for (int e = 0; e < 4; e++) {
-                        if (METRIC == 'e') { const float t = __fsub_rn(xs[e], ys[e]); ab[j] = __fadd_rn(ab[j], __fmul_rn(t, t)); }
-                        else {
-                            ab[j] = __fadd_rn(ab[j], __fmul_rn(xs[e], ys[e]));
-                            if (METRIC == 'c') { a2[j] = __fadd_rn(a2[j], __fmul_rn(xs[e], xs[e])); b2[j] = __fadd_rn(b2[j], __fmul_rn(ys[e], ys[e])); }
+                    const float2 y01 = make_float2(y.x, y.y), y23 = make_float2(y.z, y.w);
+                    if (METRIC == 'e') {
+                        const float2 t01 = sub2(x01, y01), t23 = sub2(x23, y23);
+                        const float2 p01 = mul2(t01, t01), p23 = mul2(t23, t23);
+                        ab[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(ab[j], p01.x), p01.y), p23.x), p23.y);
+                    } else {
+                        const float2 p01 = mul2(x01, y01), p23 = mul2(x23, y23);
+                        ab[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(ab[j], p01.x), p01.y), p23.x), p23.y);
+                        if (METRIC == 'c') {
+                            const float2 q01 = mul2(y01, y01), q23 = mul2(y23, y23);
+                            a2[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(a2[j], xx01.x), xx01.y), xx23.x), xx23.y);
+                            b2[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(b2[j], q01.x), q01.y), q23.x), q23.y);
                         }
                     }
                 }

@@ -845,6 +845,13 @@ static int flush_locked(gvss_index *x) {
     p.scratch = x->d_scratch;
     unsigned long long es = x->max_level < 0 ? ~0ull : (((unsigned long long)(uint32_t)x->max_level << 32) | x->entry);
     CU(cudaMemcpyAsync(x->d_entry_state, &es, 8, cudaMemcpyHostToDevice, x->stream));
+    // GVSS_BUILD_PROF=1: per-phase SM clocks summed over all inserts, and wall time of the ramp vs the final launch (stderr)
+    static const bool prof_on = [] { const char *e = getenv("GVSS_BUILD_PROF"); return e && atoi(e); }();
+    unsigned long long *d_prof = nullptr;
+    if (prof_on) { CU(cudaMalloc(&d_prof, 64)); CU(cudaMemsetAsync(d_prof, 0, 64, x->stream)); }
+    p.prof = d_prof;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+    if (prof_on) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventCreate(&ev2); cudaEventRecord(ev0, x->stream); }
     uint64_t linked = x->count - 0; // nodes already in the graph
     uint64_t ramp = 256; // in-flight inserts <= 1/256 of the linked nodes: recall within 0.005 of a sequential build (profiles/build_ramp_r1.txt)
     if (const char *e = getenv("GVSS_BUILD_RAMP")) ramp = std::max<uint64_t>(1, strtoull(e, nullptr, 10));
@@ -863,8 +870,22 @@ static int flush_locked(gvss_index *x) {
         GraphView g = view_of(x);
         g.count = (uint32_t)next_fresh;
         g.has_deleted = 0;
+        if (prof_on && conc >= max_warps) cudaEventRecord(ev1, x->stream);
         CU(launch_build(metric, g, p, (uint32_t)std::min<uint64_t>(conc, len), x->stream));
         done += len;
+    }
+    if (prof_on) {
+        cudaEventRecord(ev2, x->stream);
+        cudaEventSynchronize(ev2);
+        unsigned long long h[8] = {0};
+        cudaMemcpy(h, d_prof, 64, cudaMemcpyDeviceToHost);
+        float ms_all = 0, ms_last = 0;
+        cudaEventElapsedTime(&ms_all, ev0, ev2);
+        if (cudaEventQuery(ev1) == cudaSuccess) cudaEventElapsedTime(&ms_last, ev1, ev2);
+        const double n = h[5] ? (double)h[5] : 1.0;
+        fprintf(stderr, "[gvss build] %llu inserts, %u warps max: total %.1f ms (final persistent launch %.1f ms); clocks/insert: greedy %.0f beam %.0f refine %.0f connect %.0f reconnect %.0f\n",
+                h[5], max_warps, ms_all, ms_last, h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n);
+        cudaFree(d_prof); cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
     }
     CU(cudaMemcpyAsync(&es, x->d_entry_state, 8, cudaMemcpyDeviceToHost, x->stream));
     CU(cudaStreamSynchronize(x->stream));

@@ -62,6 +62,7 @@ struct BuildParams {
     uint32_t *locks;         // [capacity] per-node spin locks (index.hpp:3214-3224 nodes_mutexes_)
     uint32_t ef_add;
     int direct;
+    unsigned long long *prof; // optional phase clocks: [0] greedy [1] beam search [2] refine [3] connect [4] reconnect [5] inserts
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;
