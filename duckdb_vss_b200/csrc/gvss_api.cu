@@ -853,7 +853,12 @@ static int flush_locked(gvss_index *x) {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     if (prof_on) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventCreate(&ev2); cudaEventRecord(ev0, x->stream); }
     uint64_t linked = x->count - 0; // nodes already in the graph
-    uint64_t ramp = 256; // in-flight inserts <= 1/256 of the linked nodes: recall within 0.005 of a sequential build (profiles/build_ramp_r1.txt)
+    // In-flight inserts are capped at (linked nodes / ramp). Vectors inserted at the same time cannot see each other, so
+    // small graphs need a strict cap (1/256: recall within 0.005 of a sequential build at 30k vectors), while in a large
+    // build the ramp region is a small, later repaired part of the graph and 1/64 costs nothing measurable at 1M
+    // (profiles/build_ramp_r1.txt). GVSS_BUILD_RAMP overrides.
+    const uint64_t final_nodes = x->count + slots.size();
+    uint64_t ramp = std::min<uint64_t>(256, std::max<uint64_t>(64, 25600000ull / std::max<uint64_t>(final_nodes, 1)));
     if (const char *e = getenv("GVSS_BUILD_RAMP")) ramp = std::max<uint64_t>(1, strtoull(e, nullptr, 10));
     uint64_t done = 0;
     const uint64_t total = slots.size();
