@@ -8,28 +8,14 @@
 // north star allows ("otherwise they use FFMA"); it is FP32-pipe bound, not HBM bound: a 128-row tile of the base is
 // shared through shared memory by QT queries per thread.
 #include "kernels.h"
+#include "exact_common.cuh"
+#include <vector>
 
 namespace gvss {
 
 constexpr int kRows = 128;   // base rows per tile = threads per CTA
 constexpr int kDimChunk = 32; // floats per staged chunk
 constexpr int kRowStride = kDimChunk + 4; // 9 x 16 B: conflict-free per-thread float4 reads
-
-__device__ __forceinline__ uint32_t order_key(float d) {
-    if (d != d) return 0xFFFFFFFFu;           // NaN sorts last (DuckDB orders NaN as the greatest value)
-    if (d == 0.0f) return 0x80000000u;        // -0 == +0
-    const uint32_t u = __float_as_uint(d);
-    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-}
-
-template <char METRIC> __device__ __forceinline__ float fold_finish(float ab, float a2, float b2) {
-    if (METRIC == 'e') return __fsqrt_rn(ab);
-    if (METRIC == 'i') return -ab;
-    const float sim = __fdiv_rn(ab, __fsqrt_rn(__fmul_rn(a2, b2)));
-    const float mn = (1.0f < sim) ? 1.0f : sim;   // std::min(sim, 1)
-    const float mx = (-1.0f < mn) ? mn : -1.0f;   // std::max(-1, .)  (a NaN similarity ends as -1, like DuckDB)
-    return __fsub_rn(1.0f, mx);
-}
 
 // sorted insert of (key, dist) into a k-entry list owned by one warp
 __device__ __forceinline__ void list_insert(unsigned long long *lk, float *ld, uint32_t &size, uint32_t k,
@@ -280,6 +266,61 @@ cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const 
     case 'i': return run_exact<'i', 16>(base, n, keys, queries, nq, d, k, ids_out, dist_out, st);
     default: return run_exact<'e', 16>(base, n, keys, queries, nq, d, k, ids_out, dist_out, st);
     }
+}
+
+// merge of per-split candidate lists of the tensor-core path: ids = row indices (-1 = empty), "distances" = scores
+cudaError_t launch_merge_partials(const unsigned long long *pk, const float *ps, uint32_t splits, uint64_t nq, uint32_t kc, int64_t *rows_out,
+                                  float *scores_out, cudaStream_t st) {
+    if (!nq) return cudaSuccess;
+    const uint32_t wpb = 4;
+    k_merge<0><<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(pk, ps, splits, nq, kc, nullptr, rows_out, scores_out);
+    count_launch();
+    return cudaGetLastError();
+}
+
+__global__ void k_gather_rows(const float *__restrict__ src, const uint32_t *__restrict__ idx, uint64_t m, uint32_t d, float *__restrict__ dst) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m * d) dst[i] = src[(uint64_t)idx[i / d] * d + i % d];
+}
+__global__ void k_scatter_results(const int64_t *__restrict__ ids, const float *__restrict__ dist, const uint32_t *__restrict__ idx, uint64_t m,
+                                  uint32_t k, int64_t *__restrict__ ids_out, float *__restrict__ dist_out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m * k) return;
+    const uint64_t o = (uint64_t)idx[i / k] * k + i % k;
+    ids_out[o] = ids[i];
+    if (dist_out) dist_out[o] = dist[i];
+}
+
+// Recomputes the queries whose flag is set with the all-pairs exact kernel (synchronises the stream).
+cudaError_t launch_exact_topk_flagged(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries, uint64_t nq,
+                                      uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out, const uint32_t *flags, uint64_t *flagged_out,
+                                      cudaStream_t st) {
+    std::vector<uint32_t> h(nq);
+    cudaError_t e = cudaMemcpyAsync(h.data(), flags, nq * 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return e;
+    std::vector<uint32_t> idx;
+    for (uint64_t i = 0; i < nq; i++) if (h[i]) idx.push_back((uint32_t)i);
+    if (flagged_out) *flagged_out = idx.size();
+    if (idx.empty()) return cudaSuccess;
+    const uint64_t m = idx.size();
+    uint32_t *d_idx = nullptr; float *qtmp = nullptr, *dtmp = nullptr; int64_t *itmp = nullptr;
+    auto cleanup = [&]() { cudaFreeAsync(d_idx, st); cudaFreeAsync(qtmp, st); cudaFreeAsync(dtmp, st); cudaFreeAsync(itmp, st); };
+    if ((e = cudaMallocAsync(&d_idx, m * 4, st)) != cudaSuccess || (e = cudaMallocAsync(&qtmp, m * d * 4, st)) != cudaSuccess ||
+        (e = cudaMallocAsync(&dtmp, m * k * 4, st)) != cudaSuccess || (e = cudaMallocAsync(&itmp, m * k * 8, st)) != cudaSuccess) { cleanup(); return e; }
+    e = cudaMemcpyAsync(d_idx, idx.data(), m * 4, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) {
+        k_gather_rows<<<(unsigned)((m * d + 255) / 256), 256, 0, st>>>(queries, d_idx, m, d, qtmp);
+        count_launch();
+        e = launch_exact_topk(metric, base, n, keys, qtmp, m, d, k, itmp, dtmp, st);
+    }
+    if (e == cudaSuccess) {
+        k_scatter_results<<<(unsigned)((m * k + 255) / 256), 256, 0, st>>>(itmp, dtmp, d_idx, m, k, ids_out, dist_out);
+        count_launch();
+        e = cudaStreamSynchronize(st); // idx must outlive the copies above
+    }
+    cleanup();
+    return e;
 }
 
 cudaError_t launch_merge_topk(const int64_t *gk, const float *gd, uint32_t shards, uint64_t nq, uint32_t k, int64_t *keys_out,

@@ -700,7 +700,25 @@ int gvss_exact_topk_device(char metric, const float *base, uint64_t n, const int
                            uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out, void *cuda_stream) {
     if (!base || !queries || !ids_out) return fail("gvss_exact_topk_device: null buffer");
     if (!k || k > 1024) return fail("gvss_exact_topk: k must be in 1..1024");
+    // tensor-core candidates (3xTF32) + exact re-rank when the shape fits (k <= 16, enough work to fill the tiles);
+    // GVSS_EXACT_TC=0 forces the all-pairs FP32 kernel, =2 forces the tensor-core path even for tiny inputs
+    static const int tc_mode = [] { const char *e = getenv("GVSS_EXACT_TC"); return e ? atoi(e) : 1; }();
+    if (tc_mode && (tc_mode == 2 || (uint64_t)n * nq >= (1ull << 22))) {
+        const cudaError_t e = launch_exact_topk_tc(metric, base, n, keys, queries, nq, d, k, ids_out, dist_out, nullptr, nullptr, (cudaStream_t)cuda_stream);
+        if (e == cudaSuccess) return 0;
+        if (e != cudaErrorNotSupported) return fail("CUDA error %s in the tensor-core exact top-k", cudaGetErrorString(e));
+        cudaGetLastError();
+    }
     CU(launch_exact_topk(metric, base, n, keys, queries, nq, d, k, ids_out, dist_out, (cudaStream_t)cuda_stream));
+    return 0;
+}
+
+// test hook (not part of include/gvss.h): raw q·b of the tensor-core path plus the number of queries that needed the fallback
+int gvssdbg_tc_exact(char metric, const float *base, uint64_t n, const float *queries, uint64_t nq, uint32_t d, uint32_t k, int64_t *ids_out,
+                     float *dist_out, float *dots_out, uint64_t *flagged) {
+    const cudaError_t e = launch_exact_topk_tc(metric, base, n, nullptr, queries, nq, d, k, ids_out, dist_out, dots_out, flagged, nullptr);
+    if (e != cudaSuccess) return fail("tensor-core exact top-k: %s", cudaGetErrorString(e));
+    CU(cudaDeviceSynchronize());
     return 0;
 }
 

@@ -72,6 +72,15 @@ cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, u
 cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries,
                               uint64_t nq, uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out,
                               cudaStream_t stream);
+// tensor-core candidate generation + exact re-rank (exact_tc.cu); cudaErrorNotSupported = shape outside that path
+cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries, uint64_t nq,
+                                 uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out, float *dbg_dots, uint64_t *flagged_out,
+                                 cudaStream_t stream);
+cudaError_t launch_merge_partials(const unsigned long long *pk, const float *ps, uint32_t splits, uint64_t nq, uint32_t kc, int64_t *rows_out,
+                                  float *scores_out, cudaStream_t stream);
+cudaError_t launch_exact_topk_flagged(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries, uint64_t nq,
+                                      uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out, const uint32_t *flags, uint64_t *flagged_out,
+                                      cudaStream_t stream);
 cudaError_t launch_merge_topk(const int64_t *gk, const float *gd, uint32_t shards, uint64_t nq, uint32_t k,
                               int64_t *keys_out, float *dist_out, cudaStream_t stream);
 

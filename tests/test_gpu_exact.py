@@ -69,3 +69,64 @@ def test_merge_topk_orders_by_distance_then_key():
         cand = sorted((float(d[s, qi, i]), int(keys[s, qi, i])) for s in range(shards) for i in range(k) if keys[s, qi, i] >= 0)[:k]
         assert [c[1] for c in cand] == ok[qi].tolist()
         assert [c[0] for c in cand] == od[qi].tolist()
+
+
+def _tc_exact(metric, base, q, k, want_dots=False):
+    """Drives the tensor-core path directly (test hook gvssdbg_tc_exact, not part of the public ABI)."""
+    import ctypes as C
+    import torch
+    from duckdb_vss_b200.index import METRIC_CHAR
+    fn = gv.lib().gvssdbg_tc_exact
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_char, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                   C.c_void_p, C.POINTER(C.c_uint64)]
+    b, qq = torch.from_numpy(base).cuda(), torch.from_numpy(q).cuda()
+    n, nq = base.shape[0], q.shape[0]
+    ids = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    dist = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+    dots = torch.zeros((nq, n), dtype=torch.float32, device="cuda") if want_dots else None
+    flagged = C.c_uint64(0)
+    rc = fn(METRIC_CHAR[metric], b.data_ptr(), n, qq.data_ptr(), nq, base.shape[1], k, ids.data_ptr(), dist.data_ptr(),
+            dots.data_ptr() if want_dots else None, C.byref(flagged))
+    assert rc == 0, gv.lib().gvss_last_error().decode()
+    return ids.cpu().numpy(), dist.cpu().numpy(), (dots.cpu().numpy() if want_dots else None), flagged.value
+
+
+def _checker_topk(metric, base, q, k):
+    import oracle
+    if oracle.have_ref():
+        from oracle import ref
+        return ref.duckdb_topk(metric, base, q, k, threads=8)
+    from oracle import port
+    return port.exact_topk(metric, base, q, k)
+
+
+@pytest.mark.parametrize("metric,d,n,nq", [("l2sq", 128, 30000, 257), ("cosine", 768, 4000, 130), ("ip", 96, 9000, 64), ("l2sq", 20, 1500, 40)])
+def test_tensor_core_candidates_plus_rerank_are_bit_exact(metric, d, n, nq):
+    base, q = synth.clustered(n, d, 40, 8, 900 + d, nq)
+    if metric == "ip":
+        base /= np.linalg.norm(base, axis=1, keepdims=True)
+    ids, dist, dots, flagged = _tc_exact(metric, base, q, 10, want_dots=n <= 9000)
+    want_ids, want_d = _checker_topk(metric, base, q, 10)
+    np.testing.assert_array_equal(ids, want_ids)
+    np.testing.assert_array_equal(dist.view(np.uint32), want_d.view(np.uint32))
+    if dots is not None:   # 3xTF32 holds fp32 tolerance: error relative to |q||b| ~1e-6..1e-5 (grows with d through the
+        # tensor core's fp32 accumulation), far below a single TF32 pass (~5e-4)
+        ref_dots = q.astype(np.float64) @ base.astype(np.float64).T
+        scale = np.linalg.norm(q, axis=1)[:, None] * np.linalg.norm(base, axis=1)[None, :]
+        assert (np.abs(dots - ref_dots) / scale).max() < 3e-5
+    assert flagged <= nq // 20
+
+
+def test_tensor_core_path_falls_back_on_ties_it_cannot_resolve():
+    # integer grid {0,1,2}^6 padded to 8 dims, k = 16: from the centre point 12 rows sit at distance 1 and 60 at sqrt(2),
+    # so ranks 14..16 are taken from 60 tied rows — more than the 32 candidate slots. The candidate set cannot be proven
+    # sufficient -> the query is recomputed by the all-pairs kernel; the result is still exact
+    g = np.array(np.meshgrid(*[np.arange(3)] * 6, indexing="ij")).reshape(6, -1).T.astype(np.float32)
+    base = np.concatenate([g, np.zeros((g.shape[0], 2), np.float32)], axis=1)
+    q = base[[0, 364, 728]].copy()
+    ids, dist, _, flagged = _tc_exact("l2sq", base, q, 16)
+    want_ids, want_d = _checker_topk("l2sq", base, q, 16)
+    np.testing.assert_array_equal(ids, want_ids)
+    np.testing.assert_array_equal(dist.view(np.uint32), want_d.view(np.uint32))
+    assert flagged >= 1
