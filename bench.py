@@ -240,10 +240,12 @@ def main():
     truth = torch.empty((nq, k), dtype=torch.int64, device=dev)
     tdist = torch.empty((nq, k), dtype=torch.float32, device=dev)
     kdev = torch.from_numpy(keys_np).to(dev)
-    t0 = time.perf_counter()
-    gvi.exact_topk_device("l2sq", base.data_ptr(), n, q.data_ptr(), nq, d, k, truth.data_ptr(), tdist.data_ptr(), kdev.data_ptr(), stream)
-    torch.cuda.synchronize()
-    t_exact = time.perf_counter() - t0
+    t_exact = None
+    for _ in range(2):  # second call: pools and modules warm
+        t0 = time.perf_counter()
+        gvi.exact_topk_device("l2sq", base.data_ptr(), n, q.data_ptr(), nq, d, k, truth.data_ptr(), tdist.data_ptr(), kdev.data_ptr(), stream)
+        torch.cuda.synchronize()
+        t_exact = time.perf_counter() - t0
     truth_np = truth.cpu().numpy()
 
     okeys = torch.empty((nq, k), dtype=torch.int64, device=dev)
@@ -379,7 +381,8 @@ def main():
             "clocks": clocks.summary(),
             "build": {"value": build_vps, "unit": "vectors/s", "seconds": t_build, "kernel_launches": int(build_launches),
                       "note": "gvss_add_batch_device + gvss_flush, rows resident in HBM, timed once before the steps"},
-            "exact_topk": {"seconds": t_exact, "queries": nq, "base": n, "note": "ground truth, first call (includes lazy module load)"},
+            "exact_topk": {"seconds": t_exact, "queries": nq, "base": n, "queries_per_s": nq / t_exact,
+                           "note": "ground truth: tcgen05 3xTF32 candidate tiles + exact re-rank (bit-exact vs DuckDB folds), 2nd call, wall clock incl. plane split"},
             "wall_s_timed_region": t_wall,
         }
         print(json.dumps(line))

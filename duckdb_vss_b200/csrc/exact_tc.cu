@@ -28,10 +28,12 @@ namespace gvss {
 constexpr int kTM = 128;     // queries per tile (UMMA M)
 constexpr int kTN = 128;     // base rows per tile (UMMA N)
 constexpr int kKB = 32;      // floats per K block = one 128-byte swizzle row
-constexpr int kStages = 3;
+constexpr int kStages = 3;        // ring depth of the query-resident variant (32 KB stages)
+constexpr int kStagesStream = 2;  // ring depth when the query tile streams too (64 KB stages)
 constexpr int kCand = 32;    // candidates kept per query
 constexpr uint32_t kTileBytes = kTM * kKB * 4; // 16 KB per operand tile
 constexpr uint32_t kStageBytes = 4 * kTileBytes;
+constexpr int kScStride = 36;       // floats per query in the score staging area: 9 x 16 B -> conflict-free 16-byte stores
 constexpr uint32_t kTcThreads = 192; // warp 0: TMA, warp 1: MMA + TMEM alloc, warps 2-5: epilogue
 
 __device__ __forceinline__ void mbar_arrive_expect(uint64_t *bar, uint32_t bytes) { mbar_expect_tx(bar, bytes); }
@@ -61,6 +63,20 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// wait with a suspend-time hint: the epilogue warps sleep in hardware instead of spinning on issue slots
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAITR_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+        "@p bra DONER_%=;\n"
+        "bra WAITR_%=;\n"
+        "DONER_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity), "r"(2000u)
+        : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -111,14 +127,27 @@ struct TcParams {
     float *dbg_dots;              // optional [nq][n] raw q·b (validation of the tensor-core path)
 };
 
+// QRES: the query tile (hi + lo planes of every K block) stays resident in shared memory for the whole CTA and only the
+// base tiles stream through the ring — half the L2->SM traffic per tile. Needs dk <= 128 (128 KB of queries + 3 x 32 KB).
+template <bool QRES>
 __global__ void __launch_bounds__(kTcThreads, 1)
 k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__ CUtensorMap map_q_lo,
            const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo, TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *tiles = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
-    uint64_t *bars = reinterpret_cast<uint64_t *>(tiles + kStages * kStageBytes);
-    uint64_t *full = bars, *empty = bars + kStages, *acc_full = bars + 2 * kStages, *acc_empty = bars + 2 * kStages + 2;
-    uint32_t *tmem_base_smem = reinterpret_cast<uint32_t *>(bars + 2 * kStages + 4);
+    constexpr uint32_t stage_bytes = QRES ? 2 * kTileBytes : kStageBytes;   // ring stage: (B_hi, B_lo) or (Q_hi, Q_lo, B_hi, B_lo)
+    constexpr uint32_t b_off = QRES ? 0u : 2 * kTileBytes;                  // offset of B_hi inside a stage
+    constexpr uint32_t NST = QRES ? kStages : kStagesStream;
+    unsigned char *qres = tiles + NST * stage_bytes;                        // QRES: [kblock][hi, lo] tiles
+    unsigned char *after = qres + (QRES ? (p.dk / kKB) * 2 * kTileBytes : 0u);
+    float *cl_s = reinterpret_cast<float *>(after);                          // [128 queries][kCand] candidate scores, ascending
+    uint32_t *cl_r = reinterpret_cast<uint32_t *>(after + kTM * kCand * 4);  // ... and rows
+    float *sc = reinterpret_cast<float *>(after + 2 * kTM * kCand * 4);      // [128 queries][36] scores of the current 32-column chunk
+    float *bn_s = sc + kTM * kScStride;                                      // [4 epilogue warps][128] norms of the current base tile
+    uint64_t *bars = reinterpret_cast<uint64_t *>(after + 2 * kTM * kCand * 4 + kTM * kScStride * 4 + 4 * kTN * 4);
+    uint64_t *full = bars, *empty = bars + NST, *acc_full = bars + 2 * NST, *acc_empty = bars + 2 * NST + 2;
+    uint64_t *q_full = bars + 2 * NST + 4;
+    uint32_t *tmem_base_smem = reinterpret_cast<uint32_t *>(bars + 2 * NST + 5);
 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint32_t kblocks = p.dk / kKB;
@@ -128,8 +157,9 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
     const uint32_t ntiles = r_end > r_begin ? (uint32_t)((r_end - r_begin + kTN - 1) / kTN) : 0;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kStages; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (uint32_t i = 0; i < NST; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4 * 32); }
+        mbar_init(q_full, 1);
         mbar_fence_init();
     }
     if (warp == 1) { // TMEM: 2 accumulator buffers x 128 fp32 columns
@@ -144,18 +174,27 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
+            if (QRES && ntiles) {
+                mbar_arrive_expect(q_full, kblocks * 2 * kTileBytes);
+                for (uint32_t kb = 0; kb < kblocks; kb++) {
+                    tma_tile_2d(qres + (kb * 2 + 0) * kTileBytes, &map_q_hi, (int)(kb * kKB), (int)q0, q_full);
+                    tma_tile_2d(qres + (kb * 2 + 1) * kTileBytes, &map_q_lo, (int)(kb * kKB), (int)q0, q_full);
+                }
+            }
             uint32_t it = 0;
             for (uint32_t t = 0; t < ntiles; t++) {
                 const int row0 = (int)(r_begin + (uint64_t)t * kTN);
                 for (uint32_t kb = 0; kb < kblocks; kb++, it++) {
-                    const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
-                    mbar_wait(&empty[s], ph ^ 1u);
-                    unsigned char *st = tiles + s * kStageBytes;
-                    mbar_arrive_expect(&full[s], kStageBytes);
-                    tma_tile_2d(st + 0 * kTileBytes, &map_q_hi, (int)(kb * kKB), (int)q0, &full[s]);
-                    tma_tile_2d(st + 1 * kTileBytes, &map_q_lo, (int)(kb * kKB), (int)q0, &full[s]);
-                    tma_tile_2d(st + 2 * kTileBytes, &map_b_hi, (int)(kb * kKB), row0, &full[s]);
-                    tma_tile_2d(st + 3 * kTileBytes, &map_b_lo, (int)(kb * kKB), row0, &full[s]);
+                    const uint32_t s = it % NST, ph = (it / NST) & 1u;
+                    mbar_wait_relaxed(&empty[s], ph ^ 1u);
+                    unsigned char *st = tiles + s * stage_bytes;
+                    mbar_arrive_expect(&full[s], stage_bytes);
+                    if (!QRES) {
+                        tma_tile_2d(st + 0 * kTileBytes, &map_q_hi, (int)(kb * kKB), (int)q0, &full[s]);
+                        tma_tile_2d(st + 1 * kTileBytes, &map_q_lo, (int)(kb * kKB), (int)q0, &full[s]);
+                    }
+                    tma_tile_2d(st + b_off, &map_b_hi, (int)(kb * kKB), row0, &full[s]);
+                    tma_tile_2d(st + b_off + kTileBytes, &map_b_lo, (int)(kb * kKB), row0, &full[s]);
                 }
             }
         }
@@ -165,18 +204,20 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
             // kind::tf32, D = F32, A/B = TF32, both K-major, N = 128, M = 128
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTN >> 3) << 17) | ((uint32_t)(kTM >> 4) << 24);
             uint32_t it = 0;
+            if (QRES && ntiles) mbar_wait(q_full, 0);
             for (uint32_t t = 0; t < ntiles; t++) {
                 const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
-                mbar_wait(&acc_empty[buf], aph ^ 1u);
+                mbar_wait_relaxed(&acc_empty[buf], aph ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * kTN;
                 for (uint32_t kb = 0; kb < kblocks; kb++, it++) {
-                    const uint32_t s = it % kStages, ph = (it / kStages) & 1u;
-                    mbar_wait(&full[s], ph);
+                    const uint32_t s = it % NST, ph = (it / NST) & 1u;
+                    mbar_wait_relaxed(&full[s], ph);
                     tc_fence_after();
-                    unsigned char *st = tiles + s * kStageBytes;
-                    const uint64_t qh = umma_desc_sw128(st), ql = umma_desc_sw128(st + kTileBytes);
-                    const uint64_t bh = umma_desc_sw128(st + 2 * kTileBytes), bl = umma_desc_sw128(st + 3 * kTileBytes);
+                    unsigned char *st = tiles + s * stage_bytes;
+                    const unsigned char *qt = QRES ? qres + kb * 2 * kTileBytes : st;
+                    const uint64_t qh = umma_desc_sw128(qt), ql = umma_desc_sw128(qt + kTileBytes);
+                    const uint64_t bh = umma_desc_sw128(st + b_off), bl = umma_desc_sw128(st + b_off + kTileBytes);
 #pragma unroll
                     for (uint32_t k = 0; k < kKB / 8; k++) { // UMMA_K = 8 for TF32: 32 bytes along K inside the swizzle row
                         const uint64_t adv = (uint64_t)(k * 32 >> 4);
@@ -190,72 +231,98 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
             }
         }
     } else {
-        // ===== epilogue: thread <-> query row (TMEM lane) =====
+        // ===== epilogue: thread <-> query row (TMEM lane) for the scores, warp <-> query for the candidate lists =====
         const uint32_t quarter = warp & 3u;              // tcgen05.ld: a warp may touch lanes [32*(warp%4), +32)
         const uint32_t qrow = quarter * 32 + lane;
         const uint64_t qi = q0 + qrow;
         const bool qvalid = qi < p.nq;
         const float qn2 = qvalid ? p.qnorm2[qi] : 0.f;
-        float ls[kCand];
-        uint32_t lr[kCand];
-#pragma unroll
-        for (int i = 0; i < kCand; i++) { ls[i] = CUDART_INF_F; lr[i] = 0xFFFFFFFFu; }
+        // the 32 candidate lists of this warp's queries live in shared memory, one entry per lane
+        for (uint32_t qq = 0; qq < 32; qq++) {
+            cl_s[(quarter * 32 + qq) * kCand + lane] = CUDART_INF_F;
+            cl_r[(quarter * 32 + qq) * kCand + lane] = 0xFFFFFFFFu;
+        }
+        __syncwarp();
+        float worst = CUDART_INF_F; // this thread's query: score of its current worst kept candidate
         for (uint32_t t = 0; t < ntiles; t++) {
             const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
-            mbar_wait(&acc_full[buf], aph);
+            mbar_wait_relaxed(&acc_full[buf], aph);
             tc_fence_after();
             const uint64_t row0 = r_begin + (uint64_t)t * kTN;
+            // norms of this tile's 128 base rows, staged once per warp (zero beyond the end: those columns never pass)
+            float *bnw = bn_s + quarter * kTN;
+            for (uint32_t c = lane; c < (uint32_t)kTN; c += 32) bnw[c] = row0 + c < r_end ? __ldg(&p.bnorm2[row0 + c]) : 0.f;
+            __syncwarp();
+            const uint32_t valid_cols = (uint32_t)min((uint64_t)kTN, r_end - row0);
             for (uint32_t c0 = 0; c0 < kTN; c0 += 32) {
                 float acc[32];
                 tmem_ld32(tmem_base + ((quarter * 32u) << 16) + buf * kTN + c0, acc);
-                // phase 1 (straight-line): scores of the 32 columns and the set of those that beat this query's threshold.
-                // Keeping the (rare) insertion out of the unrolled loop keeps the loop inside the instruction cache.
+                if (p.dbg_dots && qvalid) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) if (c0 + j < valid_cols) p.dbg_dots[qi * p.n + row0 + c0 + j] = acc[j];
+                }
+                // phase 1 (straight-line, thread <-> query): scores of 32 columns into shared memory, bit mask of the
+                // columns that beat this query's threshold
                 uint32_t pass = 0;
-                const float worst = ls[kCand - 1];
 #pragma unroll
-                for (int j = 0; j < 32; j++) {
-                    const uint64_t row = row0 + c0 + j;
-                    const bool in = row < r_end && qvalid;
-                    const float bn = in ? __ldg(&p.bnorm2[row]) : 0.f;
-                    if (p.dbg_dots && in) p.dbg_dots[qi * p.n + row] = acc[j];
-                    float s;
-                    if (p.metric == 'e') s = fmaf(-2.f, acc[j], bn);
-                    else if (p.metric == 'i') s = -acc[j];
-                    else s = -acc[j] * rsqrtf(fmaxf(qn2 * bn, 1e-30f));
-                    acc[j] = s;
-                    pass |= (in && s < worst) ? (1u << j) : 0u;
-                }
-                // phase 2: sorted insertion of the few that passed (equal scores keep the earlier row first)
-                while (pass) {
-                    const int j = __ffs(pass) - 1;
-                    pass &= pass - 1;
-                    float s = acc[0];
+                for (int j4 = 0; j4 < 8; j4++) {
+                    const float4 bn = *reinterpret_cast<const float4 *>(bnw + c0 + j4 * 4);
+                    const float b4[4] = {bn.x, bn.y, bn.z, bn.w};
+                    float s4[4];
 #pragma unroll
-                    for (int i = 1; i < 32; i++) s = (j == i) ? acc[i] : s;
-                    if (!(s < ls[kCand - 1])) continue;
-                    const uint32_t row = (uint32_t)(row0 + c0 + j);
-                    bool placed = false;
-#pragma unroll
-                    for (int i = kCand - 1; i >= 1; --i) {
-                        if (!placed) {
-                            if (ls[i - 1] > s) { ls[i] = ls[i - 1]; lr[i] = lr[i - 1]; }
-                            else { ls[i] = s; lr[i] = row; placed = true; }
-                        }
+                    for (int e = 0; e < 4; e++) {
+                        const float a = acc[j4 * 4 + e];
+                        if (p.metric == 'e') s4[e] = fmaf(-2.f, a, b4[e]);
+                        else if (p.metric == 'i') s4[e] = -a;
+                        else s4[e] = -a * rsqrtf(fmaxf(qn2 * b4[e], 1e-30f));
+                        pass |= (s4[e] < worst) ? (1u << (j4 * 4 + e)) : 0u;
                     }
-                    if (!placed) { ls[0] = s; lr[0] = row; }
+                    *reinterpret_cast<float4 *>(sc + qrow * kScStride + j4 * 4) = make_float4(s4[0], s4[1], s4[2], s4[3]);
                 }
+                const uint32_t colmask = valid_cols >= c0 + 32 ? 0xFFFFFFFFu : (valid_cols > c0 ? (1u << (valid_cols - c0)) - 1u : 0u);
+                pass = qvalid ? (pass & colmask) : 0u;
+                __syncwarp();
+                // phase 2 (warp <-> query): sorted insertion with one ballot and one shuffle per candidate; equal scores
+                // keep the earlier row first
+                uint32_t qmask = __ballot_sync(kFull, pass != 0u);
+                while (qmask) {
+                    const uint32_t qq = __ffs(qmask) - 1;
+                    qmask &= qmask - 1;
+                    uint32_t pm = __shfl_sync(kFull, pass, qq);
+                    float *ls = cl_s + (quarter * 32 + qq) * kCand;
+                    uint32_t *lr = cl_r + (quarter * 32 + qq) * kCand;
+                    float e = ls[lane];
+                    uint32_t r = lr[lane];
+                    while (pm) {
+                        const uint32_t j = __ffs(pm) - 1;
+                        pm &= pm - 1;
+                        const float s = sc[(quarter * 32 + qq) * kScStride + j];
+                        const uint32_t pos = __popc(__ballot_sync(kFull, e <= s));
+                        if (pos >= (uint32_t)kCand) continue;
+                        const float eu = __shfl_up_sync(kFull, e, 1);
+                        const uint32_t ru = __shfl_up_sync(kFull, r, 1);
+                        if (lane > pos) { e = eu; r = ru; }
+                        else if (lane == pos) { e = s; r = (uint32_t)(row0 + c0 + j); }
+                    }
+                    ls[lane] = e;
+                    lr[lane] = r;
+                    const float w31 = __shfl_sync(kFull, e, kCand - 1);
+                    if (lane == qq) worst = w31;
+                }
+                __syncwarp();
             }
             tc_fence_before();
             mbar_arrive(&acc_empty[buf]);
         }
-        if (qvalid) {
-            const size_t o = ((size_t)blockIdx.y * p.nq + qi) * kCand;
-#pragma unroll
-            for (int i = 0; i < kCand; i++) {
-                const bool have = lr[i] != 0xFFFFFFFFu;
-                p.part_key[o + i] = have ? (((unsigned long long)order_key_f(ls[i]) << 32) | lr[i]) : ~0ull;
-                p.part_score[o + i] = have ? ls[i] : CUDART_INF_F;
-            }
+        for (uint32_t qq = 0; qq < 32; qq++) { // lists out: warp-wide, one entry per lane
+            const uint64_t q = q0 + quarter * 32 + qq;
+            if (q >= p.nq) break;
+            const size_t o = ((size_t)blockIdx.y * p.nq + q) * kCand;
+            const float e = cl_s[(quarter * 32 + qq) * kCand + lane];
+            const uint32_t r = cl_r[(quarter * 32 + qq) * kCand + lane];
+            const bool have = r != 0xFFFFFFFFu;
+            p.part_key[o + lane] = have ? (((unsigned long long)order_key_f(e) << 32) | r) : ~0ull;
+            p.part_score[o + lane] = have ? e : CUDART_INF_F;
         }
     }
     tc_fence_before();
@@ -398,6 +465,19 @@ cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, con
                                  cudaStream_t st) {
     if (k == 0 || k > 16 || n < 1 || d < 4 || n >= 0xFFFFFFFFull || !get_encode()) return cudaErrorNotSupported;
     const uint32_t dk = (d + kKB - 1) / kKB * kKB;
+    {   // keep the stream-ordered pool's memory between calls (the planes below are > 1 GB at 1M x 128)
+        static bool pool_set[64];
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !pool_set[dev]) {
+            cudaMemPool_t pool;
+            if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+                uint64_t keep = ~0ull;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            }
+            pool_set[dev] = true;
+        }
+    }
     DevBuf b_hi(st), b_lo(st), q_hi(st), q_lo(st), bn2(st), qn2(st), pk(st), ps(st), ck(st), cs(st), fl(st), mx(st);
     cudaError_t e;
 #define TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
@@ -415,9 +495,15 @@ cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, con
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const uint64_t qtiles = (nq + kTM - 1) / kTM, tiles = (n + kTN - 1) / kTN;
-    uint64_t splits = qtiles >= (uint64_t)sms ? 1 : ((uint64_t)sms + qtiles - 1) / qtiles;
-    if (splits > tiles) splits = tiles;
-    if (splits > 512) splits = 512;
+    // one CTA per SM (shared memory): pick the split count whose last wave wastes the least — minimise
+    // waves(qtiles * splits) / splits, the time in units of "one CTA scans the whole base"
+    uint64_t splits = 1;
+    double best = 1e30;
+    for (uint64_t sp = 1; sp <= 64 && sp <= tiles; sp++) {
+        const uint64_t waves = (qtiles * sp + sms - 1) / sms;
+        const double cost = (double)waves / (double)sp + 0.002 * (double)sp; // small bias towards fewer partial lists
+        if (cost < best) { best = cost; splits = sp; }
+    }
     const uint64_t rows_per_split = ((tiles + splits - 1) / splits) * kTN;
     splits = (n + rows_per_split - 1) / rows_per_split;
     TRY(pk.alloc(splits * nq * kCand * 8)); TRY(ps.alloc(splits * nq * kCand * 4));
@@ -426,9 +512,16 @@ cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, con
     p.n = n; p.nq = nq; p.rows_per_split = rows_per_split; p.dk = dk; p.metric = metric;
     p.bnorm2 = bn2.as<float>(); p.qnorm2 = qn2.as<float>();
     p.part_key = pk.as<unsigned long long>(); p.part_score = ps.as<float>(); p.dbg_dots = dbg_dots;
-    const size_t smem = (size_t)kStages * kStageBytes + 1024 + 256;
-    TRY(cudaFuncSetAttribute(k_tiles_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_tiles_tc<<<dim3((unsigned)qtiles, (unsigned)splits), kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
+    const bool qres = dk <= 64; // query tile resident: 2*dk/32 tiles of 16 KB next to 3 x 32 KB stages and 48 KB of lists
+    const size_t lists = 2 * (size_t)kTM * kCand * 4 + (size_t)kTM * kScStride * 4 + 4 * (size_t)kTN * 4; // lists + scores + norms
+    const size_t smem = (qres ? (size_t)kStages * 2 * kTileBytes + (size_t)(dk / kKB) * 2 * kTileBytes : (size_t)kStagesStream * kStageBytes) + lists + 1024 + 256;
+    if (qres) {
+        TRY(cudaFuncSetAttribute(k_tiles_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tiles_tc<true><<<dim3((unsigned)qtiles, (unsigned)splits), kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
+    } else {
+        TRY(cudaFuncSetAttribute(k_tiles_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tiles_tc<false><<<dim3((unsigned)qtiles, (unsigned)splits), kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
+    }
     count_launch();
     TRY(cudaGetLastError());
     // merge the splits into one candidate list per query (rows as ids, scores as "distances")
