@@ -142,7 +142,7 @@ def run_reference(args):
     print(json.dumps(line))
 
 
-def cpu_baseline(args, blob_getter, q, ef, truth):
+def cpu_baseline(args, blob_getter, q, ef, truth, gpu_keys=None):
     """Reference usearch (oracle/_ref) on the host cores: search on the SAME (GPU-built) graph, build on a bounded sample."""
     try:
         import oracle
@@ -166,6 +166,7 @@ def cpu_baseline(args, blob_getter, q, ef, truth):
         r = ix.search_batch(q[:nq], 10, ef, threads=threads)
         dt = time.perf_counter() - t0
         rec = synth.recall_at_k(r["keys"], truth[:nq])
+        ids_same = bool(gpu_keys is not None and np.array_equal(r["keys"], gpu_keys[:nq]))
         # build sample: first min(n, 2500*T) vectors with the extension's thread pattern
         nb = min(args.n, max(20000, 1500 * threads)) if kind == "reference" else 3000
         base_s, _ = synth.clustered(nb, args.dims, max(1024, nb // 100), 16, 42, 0)
@@ -177,6 +178,7 @@ def cpu_baseline(args, blob_getter, q, ef, truth):
         return {"value": nq / dt, "unit": "queries/s", "cores": threads, "kind": kind,
                 "sample": f"{nq} queries, ef={ef}, on the GPU-built 1M graph loaded from its usearch stream (load {t_load:.1f}s); "
                           f"build timed on the first {nb} vectors", "recall_at_10": rec,
+                "ids_identical_to_gpu_on_same_graph": ids_same,
                 "build_vectors_per_s": nb / tb}
     except Exception as e:  # the baseline must never take the product number down
         return {"value": None, "unit": "queries/s", "cores": 0, "kind": "unavailable", "sample": repr(e)}
@@ -357,7 +359,7 @@ def main():
         achieved = algo_bytes / t_kernel / 1e9
         cpu = None
         if world == 1 and not args.no_cpu:
-            cpu = cpu_baseline(args, ix.save, q_np, ef, truth_np)
+            cpu = cpu_baseline(args, ix.save, q_np, ef, truth_np, gpu_keys=kh.numpy())
         units = world * nq * args.steps
         line = {
             "metric": METRIC, "value": units / t_dev, "unit": "queries/s", "n_gpus": world, "steps": args.steps,

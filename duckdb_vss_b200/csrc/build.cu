@@ -27,6 +27,8 @@ __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, cons
     w.top_s = reinterpret_cast<uint32_t *>(smem + sm.off_top_s);
     w.rstride = sm.rstride;
     w.stage_rows = sm.stage_rows;
+    w.chunk = sm.chunk;
+    w.nbuf = sm.nbuf;
     w.nb = reinterpret_cast<uint32_t *>(smem + sm.off_nb);
     w.nd = reinterpret_cast<float *>(smem + sm.off_nd);
     w.heap_smem = sm.heap_smem;

@@ -180,6 +180,11 @@ static uint32_t search_stage_rows() {
     }();
     return rows;
 }
+// floats of a row staged per step on the search path (GVSS_STAGE_CHUNK: 32/64/128)
+static uint32_t search_stage_chunk() {
+    static uint32_t v = [] { const char *e = getenv("GVSS_STAGE_CHUNK"); const uint32_t c = e ? (uint32_t)atoi(e) : 64u; return (c == 32u || c == 64u || c == 128u) ? c : 64u; }();
+    return v;
+}
 // query-to-node distances: 0 = rows staged in shared memory by TMA bulk copies (default: faster once the base set
 // exceeds L2, profiles/r1_search_ncu_summary.txt), 1 = rows streamed straight into registers (256-bit loads, no staging). GVSS_DIRECT_ROWS overrides for A/B measurements.
 static bool direct_rows() {
@@ -210,7 +215,7 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false);
     p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
@@ -427,7 +432,7 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     p.trace_query = -1;
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false);
     p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
     const uint32_t resident = resident_warps(x->device, p.sm.bytes, false);
     if (!resident) return fail("gvss: no CUDA device");

@@ -59,7 +59,9 @@ struct WarpWs {
     float *c;            // 2 × kChunk floats: streamed "left-hand" row chunk for node-to-node distances
     float *stage[2];     // 2 × stage_rows × rstride floats (second buffer only when dpad > kChunk)
     uint32_t rstride;    // floats between staged rows (odd multiple of 4 floats -> conflict-free LDS.128)
-    uint32_t stage_rows; // 32 (build: lane <-> candidate) or 16 (search: smaller footprint, more resident warps)
+    uint32_t stage_rows; // rows of one stage buffer: 32 (lane <-> row) or 16
+    uint32_t chunk;      // floats of a row staged per step (<= kChunk): 64 halves the footprint of a 32-row stage
+    uint32_t nbuf;       // 2 = chunks double-buffered (rows longer than one chunk), 1 = chunks staged one after the other
     bool spec_prefetch;  // prefetch every neighbour's row to L2 before the visited test resolves (trades HBM traffic for latency)
     bool direct;         // query-to-node distances stream each lane's row straight into registers (no staging)
     uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
@@ -238,7 +240,9 @@ template <int METRIC>
 __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, LeftSrc left, uint32_t my_slot,
                                                 bool active, uint32_t &staged) {
     const uint32_t lane = lane_id();
-    const uint32_t nchunks = (g.dpad + kChunk - 1) / kChunk;
+    const uint32_t chunk = w.chunk;
+    const uint32_t nchunks = (g.dpad + chunk - 1) / chunk;
+    const bool dbuf = w.nbuf == 2;
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
@@ -259,9 +263,9 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
         Acc acc = {0.0f, 0.0f, 0.0f};
 
         auto issue = [&](uint32_t ch) {
-            const uint32_t buf = ch & 1u;
-            const uint32_t off = ch * kChunk;
-            const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
+            const uint32_t buf = dbuf ? (ch & 1u) : 0u;
+            const uint32_t off = ch * chunk;
+            const uint32_t nfl = min(chunk, g.dpad - off);
             const bool need = act && !(cacheable && staged == my_slot);
             const uint32_t need_mask = __ballot_sync(kFull, need);
             const uint32_t ncopy = __popc(need_mask) + (stream_left ? 1u : 0u);
@@ -289,9 +293,9 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
 
         bool pending = issue(0);
         for (uint32_t ch = 0; ch < nchunks; ch++) {
-            const uint32_t buf = ch & 1u;
+            const uint32_t buf = dbuf ? (ch & 1u) : 0u;
             bool pending_next = false;
-            if (ch + 1 < nchunks) pending_next = issue(ch + 1);
+            if (dbuf && ch + 1 < nchunks) pending_next = issue(ch + 1);
             if (pending) {
 #if GVSS_USE_TMA
                 if (buf) { mbar_wait(w.mbar + 1, w.phase[1]); w.phase[1] ^= 1u; }
@@ -301,14 +305,15 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
                 __syncwarp();
 #endif
             }
-            const uint32_t off = ch * kChunk;
-            const uint32_t nfl = min((uint32_t)kChunk, g.dpad - off);
+            const uint32_t off = ch * chunk;
+            const uint32_t nfl = min(chunk, g.dpad - off);
             if (act) {
                 const float4 *a = reinterpret_cast<const float4 *>(stream_left ? (w.c + buf * kChunk) : (left.smem + off));
                 const float4 *b = reinterpret_cast<const float4 *>((buf ? w.stage[1] : w.stage[0]) + row * w.rstride);
                 acc_chunk<METRIC>(acc, a, b, (int)(nfl / 4));
             }
             __syncwarp(); // all lanes are done reading this buffer before it is refilled
+            if (!dbuf && ch + 1 < nchunks) pending_next = issue(ch + 1);
             pending = pending_next;
         }
         if (act) {

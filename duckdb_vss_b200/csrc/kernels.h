@@ -10,12 +10,14 @@ namespace gvss {
 // shared-memory carve-out of one warp (one CTA = one warp, so a CTA never needs __syncthreads)
 struct SmemLayout {
     uint32_t off_mbar, off_stage0, off_stage1, off_c, off_q, off_heap, off_top_d, off_top_s, off_nb, off_nd, off_misc;
-    uint32_t rstride, stage_rows, heap_smem, top_cap, bytes;
+    uint32_t rstride, stage_rows, chunk, nbuf, heap_smem, top_cap, bytes;
 };
 // stage_rows: 32 or 16; with_left: room for a streamed left-hand row chunk (node-to-node distances, build only);
 // list_cap: longest neighbour list (max(M, M0))
+// chunk: floats of a row staged per step (0 = default min(dpad, 128)); double_buffer: two stage buffers when a row spans
+// several chunks (build), else the chunks are staged one after the other into one buffer (search: half the footprint)
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap);
+                            bool with_left, uint32_t list_cap, uint32_t chunk = 0, bool double_buffer = true);
 uint32_t default_heap_smem(uint32_t beam);
 
 // global scratch of one warp: visited table (vis_slots u32) followed by the queue overflow (heap_ovf Cand)

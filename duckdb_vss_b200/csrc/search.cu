@@ -21,6 +21,8 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
     w.top_s = reinterpret_cast<uint32_t *>(smem + sm.off_top_s);
     w.rstride = sm.rstride;
     w.stage_rows = sm.stage_rows ? sm.stage_rows : 32u;
+    w.chunk = sm.chunk;
+    w.nbuf = sm.nbuf;
     w.nb = reinterpret_cast<uint32_t *>(smem + sm.off_nb);
     w.nd = reinterpret_cast<float *>(smem + sm.off_nd);
     w.heap_smem = sm.heap_smem;
@@ -88,13 +90,16 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
 }
 
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap) {
+                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer) {
     SmemLayout s{};
-    const uint32_t chunkf = dpad < (uint32_t)kChunk ? dpad : (uint32_t)kChunk;
+    if (chunk == 0 || chunk > (uint32_t)kChunk) chunk = (uint32_t)kChunk;
+    const uint32_t chunkf = dpad < chunk ? dpad : chunk;
+    s.chunk = chunkf;
     s.rstride = chunkf + (((chunkf / 4) % 2 == 0) ? 4u : 0u); // odd number of 16-byte granules per row
     s.stage_rows = stage_rows;
     const uint32_t stage_bytes = stage_rows * s.rstride * 4u;
-    const bool two = dpad > (uint32_t)kChunk;
+    const bool two = double_buffer && dpad > chunkf;
+    s.nbuf = two ? 2u : 1u;
     uint32_t off = 0;
     auto take = [&](uint32_t bytes, uint32_t align) { off = (off + align - 1) / align * align; uint32_t o = off; off += bytes; return o; };
     s.off_mbar = take(16, 16);
