@@ -96,3 +96,20 @@ def test_incremental_append_delete_and_slot_reuse(checker):
     p.load(ix.save())
     k2 = p.search_batch(base[500:503], 1, 64)["keys"]
     assert list(k2[:, 0]) == [500, 501, 502]
+
+
+@pytest.mark.parametrize("metric,d,n,M", [("cosine", 200, 500, 8), ("l2sq", 768, 300, 6), ("ip", 130, 400, 5)])
+def test_sequential_gpu_build_long_rows_is_byte_identical(metric, d, n, M, checker):
+    # rows longer than one staged chunk: the double-buffered multi-chunk paths of the build kernel (beam search,
+    # neighbour selection with streamed left-hand rows, re-pruning) against a single-thread reference build
+    Checker, _ = checker
+    base, _ = synth.clustered(n, d, 12, 6, 700 + d, 0)
+    ref = Checker(d, metric, M=M, ef_construction=40)
+    ref.reserve(n, 1)
+    ref.add_bulk(base, threads=1)
+    ix = gv.Index(d, metric, M=M, ef_construction=40)
+    ix.reserve(n, 1)
+    ix.set_build_concurrency(1)
+    ix.add_batch(base)
+    ix.flush()
+    assert ix.save() == ref.save()
