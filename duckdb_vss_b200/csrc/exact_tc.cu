@@ -246,12 +246,17 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
         float worst = CUDART_INF_F; // this thread's query: score of its current worst kept candidate
         for (uint32_t t = 0; t < ntiles; t++) {
             const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
+            const uint64_t row0 = r_begin + (uint64_t)t * kTN;
+            // norms of this tile's 128 base rows: loaded before the wait on the accumulator so that the L2 round trip
+            // overlaps it, staged once per warp (zero beyond the end: those columns never pass)
+            float bnr[kTN / 32];
+#pragma unroll
+            for (int c = 0; c < kTN / 32; c++) bnr[c] = row0 + c * 32 + lane < r_end ? __ldg(&p.bnorm2[row0 + c * 32 + lane]) : 0.f;
             mbar_wait_relaxed(&acc_full[buf], aph);
             tc_fence_after();
-            const uint64_t row0 = r_begin + (uint64_t)t * kTN;
-            // norms of this tile's 128 base rows, staged once per warp (zero beyond the end: those columns never pass)
             float *bnw = bn_s + quarter * kTN;
-            for (uint32_t c = lane; c < (uint32_t)kTN; c += 32) bnw[c] = row0 + c < r_end ? __ldg(&p.bnorm2[row0 + c]) : 0.f;
+#pragma unroll
+            for (int c = 0; c < kTN / 32; c++) bnw[c * 32 + lane] = bnr[c];
             __syncwarp();
             const uint32_t valid_cols = (uint32_t)min((uint64_t)kTN, r_end - row0);
             for (uint32_t c0 = 0; c0 < kTN; c0 += 32) {
