@@ -40,7 +40,7 @@ def test_add_from_host_threads_then_search():
     assert st["nodes"] == 729 and st["max_edges"] == 729 * 16   # swapped quirk, SURVEY App. A
 
 
-@pytest.mark.parametrize("metric,d,n", [("l2sq", 128, 30000), ("cosine", 64, 20000), ("ip", 96, 20000)])
+@pytest.mark.parametrize("metric,d,n", [("l2sq", 128, 30000), ("cosine", 64, 20000), ("ip", 96, 20000), ("cosine", 768, 6000)])
 def test_concurrent_gpu_build_recall_parity(metric, d, n, checker):
     Checker, kind = checker
     base, q = synth.clustered(n, d, max(64, n // 100), 16, 300 + d, 500)
