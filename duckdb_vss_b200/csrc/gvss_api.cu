@@ -191,6 +191,11 @@ static bool direct_rows() {
     static bool on = [] { const char *e = getenv("GVSS_DIRECT_ROWS"); return GVSS_DIRECT_PATH && e ? atoi(e) != 0 : false; }();
     return on;
 }
+// row staging engine: 1 = TMA bulk copies (one UBLKCP per row chunk), 0 = coalesced 16-byte cp.async (GVSS_USE_TMA)
+static bool stage_with_tma() {
+    static bool on = [] { const char *e = getenv("GVSS_USE_TMA"); return e ? atoi(e) != 0 : true; }();
+    return on;
+}
 // prefetch every listed neighbour's row to L2 before the visited test resolves (GVSS_SPEC_PREFETCH=0/1)
 static bool spec_prefetch() {
     static bool on = [] { const char *e = getenv("GVSS_SPEC_PREFETCH"); return e ? atoi(e) != 0 : false; }();
@@ -216,7 +221,7 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false);
-    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
+    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
     if (grid > nq) grid = (uint32_t)nq;
@@ -433,7 +438,7 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false);
-    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
+    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
     const uint32_t resident = resident_warps(x->device, p.sm.bytes, false);
     if (!resident) return fail("gvss: no CUDA device");
     char err[384];
@@ -861,7 +866,7 @@ static int flush_locked(gvss_index *x) {
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
     p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
     p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, 32, true, cmax);
-    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0);
+    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
     if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) { cudaFree(d_slots); return 1; }

@@ -4,7 +4,7 @@
 // (__fmul_rn/__fadd_rn, never contracted into FMA) computed by ONE lane over a whole row, so its bits equal
 // the reference's scalar loops on x86-64 (usearch index_plugins.hpp:981-993 ip, :1006-1026 cos, :1037-1052 l2sq).
 // Rows are brought from HBM into shared memory by TMA bulk copies (cp.async.bulk, 16-byte granules, mbarrier
-// completion) — or, when compiled with GVSS_USE_TMA=0, by coalesced 16-byte cp.async — into a padded layout
+// completion) — or, with WarpWs::use_tma off (GVSS_USE_TMA=0), by coalesced 16-byte cp.async — into a padded layout
 // that makes the per-lane float4 reads bank-conflict free; 32 neighbours are evaluated at once, lane i <-> row i.
 //
 // Control flow contract: the candidate queue (`next`), the result list (`top`) and the acceptance test replay
@@ -17,9 +17,6 @@
 #include <stdint.h>
 #include <stdio.h>
 
-#ifndef GVSS_USE_TMA
-#define GVSS_USE_TMA 1
-#endif
 // Alternative row path kept for A/B measurements only (build with -DGVSS_DIRECT_PATH=1, run with GVSS_DIRECT_ROWS=1):
 // every lane streams its own row into registers with 256-bit loads, no shared-memory staging. It costs 128 registers per
 // thread and lost to TMA staging once the base set exceeds L2 (profiles/r1_search_ncu_summary.txt).
@@ -62,6 +59,7 @@ struct WarpWs {
     uint32_t stage_rows; // rows of one stage buffer: 32 (lane <-> row) or 16
     uint32_t chunk;      // floats of a row staged per step (<= kChunk): 64 halves the footprint of a 32-row stage
     uint32_t nbuf;       // 2 = chunks double-buffered (rows longer than one chunk), 1 = chunks staged one after the other
+    bool use_tma;        // rows staged by TMA bulk copies (cp.async.bulk) or by coalesced 16-byte cp.async
     bool spec_prefetch;  // prefetch every neighbour's row to L2 before the visited test resolves (trades HBM traffic for latency)
     bool direct;         // query-to-node distances stream each lane's row straight into registers (no staging)
     uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
@@ -271,23 +269,38 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
             const uint32_t ncopy = __popc(need_mask) + (stream_left ? 1u : 0u);
             if (ncopy == 0) return false;
             float *sbuf = buf ? w.stage[1] : w.stage[0];
-#if GVSS_USE_TMA
-            uint64_t *bar = w.mbar + buf;
-            if (lane == 0) mbar_expect_tx(bar, ncopy * nfl * 4u);
-            __syncwarp();
-            if (need) tma_row(sbuf + row * w.rstride, g.vectors + (size_t)my_slot * g.dpad + off, nfl * 4u, bar);
-            if (stream_left && lane == 0)
-                tma_row(w.c + buf * kChunk, g.vectors + (size_t)left.slot * g.dpad + off, nfl * 4u, bar);
-#else
-            for (uint32_t m = need_mask; m; m &= m - 1) {
-                const uint32_t src = __ffs(m) - 1;
-                const uint32_t s = __shfl_sync(kFull, my_slot, src);
-                if (lane * 4 < nfl) cp_async16(sbuf + (src & (rows - 1)) * w.rstride + lane * 4, g.vectors + (size_t)s * g.dpad + off + lane * 4);
+            if (w.use_tma) {
+                uint64_t *bar = w.mbar + buf;
+                if (lane == 0) mbar_expect_tx(bar, ncopy * nfl * 4u);
+                __syncwarp();
+                if (need) tma_row(sbuf + row * w.rstride, g.vectors + (size_t)my_slot * g.dpad + off, nfl * 4u, bar);
+                if (stream_left && lane == 0)
+                    tma_row(w.c + buf * kChunk, g.vectors + (size_t)left.slot * g.dpad + off, nfl * 4u, bar);
+            } else {
+                // coalesced 16-byte cp.async (LDGSTS): one instruction moves 32 granules = 32*4/nfl rows of this chunk
+                const uint32_t gpr = nfl / 4;                 // 16-byte granules per row chunk (<= 32)
+                const uint32_t rpi = 32u / gpr;               // rows per instruction
+                const uint32_t sub = lane / gpr, gi = lane % gpr;
+                const bool prefix = (need_mask & (need_mask + 1u)) == 0u && (need_mask & 1u); // lanes 0..cnt-1 (pass 0)
+                if (prefix) {
+                    const uint32_t cnt = __popc(need_mask);
+                    for (uint32_t r0 = 0; r0 < cnt; r0 += rpi) {
+                        const uint32_t src = r0 + sub;        // lane that owns the row this lane helps to copy
+                        const bool ok = sub < rpi && src < cnt;
+                        const uint32_t s = __shfl_sync(kFull, my_slot, ok ? src : 0);
+                        if (ok) cp_async16(sbuf + src * w.rstride + gi * 4, g.vectors + (size_t)s * g.dpad + off + gi * 4);
+                    }
+                } else {
+                    for (uint32_t m = need_mask; m; m &= m - 1) {
+                        const uint32_t src = __ffs(m) - 1;
+                        const uint32_t s = __shfl_sync(kFull, my_slot, src);
+                        if (lane < gpr) cp_async16(sbuf + (src & (rows - 1)) * w.rstride + lane * 4, g.vectors + (size_t)s * g.dpad + off + lane * 4);
+                    }
+                }
+                if (stream_left && lane < gpr)
+                    cp_async16(w.c + buf * kChunk + lane * 4, g.vectors + (size_t)left.slot * g.dpad + off + lane * 4);
+                cp_async_commit();
             }
-            if (stream_left && lane * 4 < nfl)
-                cp_async16(w.c + buf * kChunk + lane * 4, g.vectors + (size_t)left.slot * g.dpad + off + lane * 4);
-            cp_async_commit();
-#endif
             return true;
         };
 
@@ -297,13 +310,13 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
             bool pending_next = false;
             if (dbuf && ch + 1 < nchunks) pending_next = issue(ch + 1);
             if (pending) {
-#if GVSS_USE_TMA
-                if (buf) { mbar_wait(w.mbar + 1, w.phase[1]); w.phase[1] ^= 1u; }
-                else { mbar_wait(w.mbar, w.phase[0]); w.phase[0] ^= 1u; }
-#else
-                if (pending_next) cp_async_wait<1>(); else cp_async_wait<0>();
-                __syncwarp();
-#endif
+                if (w.use_tma) {
+                    if (buf) { mbar_wait(w.mbar + 1, w.phase[1]); w.phase[1] ^= 1u; }
+                    else { mbar_wait(w.mbar, w.phase[0]); w.phase[0] ^= 1u; }
+                } else {
+                    if (pending_next) cp_async_wait<1>(); else cp_async_wait<0>();
+                    __syncwarp();
+                }
             }
             const uint32_t off = ch * chunk;
             const uint32_t nfl = min(chunk, g.dpad - off);

@@ -11,6 +11,7 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
                                       const ScratchLayout &sl, int direct) {
     w.direct = (direct & 1) != 0;
     w.spec_prefetch = (direct & 2) != 0;
+    w.use_tma = (direct & 4) == 0;
     w.mbar = reinterpret_cast<uint64_t *>(smem + sm.off_mbar);
     w.stage[0] = reinterpret_cast<float *>(smem + sm.off_stage0);
     w.stage[1] = reinterpret_cast<float *>(smem + sm.off_stage1);
