@@ -224,6 +224,8 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
+    static const uint32_t max_warps = [] { const char *e = getenv("GVSS_SEARCH_MAX_WARPS"); return e ? (uint32_t)atoi(e) : 0u; }();
+    if (max_warps && grid > max_warps) grid = max_warps; // experiment knob: fewer resident queries = smaller visited-table footprint
     if (grid > nq) grid = (uint32_t)nq;
     if (ensure_scratch(x, p.sl.bytes_per_warp * grid)) return 1;
     p.scratch = x->d_scratch;
@@ -865,7 +867,8 @@ static int flush_locked(gvss_index *x) {
     const uint32_t cmax = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
     p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
-    p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, 32, true, cmax);
+    static const uint32_t build_rows = [] { const char *e = getenv("GVSS_BUILD_STAGE_ROWS"); const uint32_t v = e ? (uint32_t)atoi(e) : 32u; return v == 16u ? 16u : 32u; }();
+    p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, build_rows, true, cmax);
     p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
