@@ -141,3 +141,60 @@ def test_device_resident_search_matches_host_path():
     torch.cuda.synchronize()
     np.testing.assert_array_equal(keys.cpu().numpy(), z["keys_ef64"])
     np.testing.assert_array_equal(dist.cpu().numpy().view(np.uint32), z["dist_ef64"].view(np.uint32))
+
+
+def test_tiny_connectivity_options_build_and_search_like_the_reference(checker):
+    # hnsw_options.test:49-50 accepts ef_construction=100, ef_search=100, M=3, M0=3
+    Checker, _ = checker
+    base, q = synth.clustered(700, 5, 10, 3, 21, 50)
+    ref = Checker(5, "l2sq", M=3, M0=3, ef_construction=100, ef_search=100)
+    ref.reserve(700, 1)
+    ref.add_bulk(base, threads=1)
+    ix = gv.Index(5, "l2sq", M=3, M0=3, ef_construction=100, ef_search=100)
+    ix.reserve(700, 1)
+    ix.set_build_concurrency(1)
+    ix.add_batch(base)
+    ix.flush()
+    assert ix.save() == ref.save()
+    want = ref.search_batch(q, 3, 100)
+    keys, dist, counts = ix.ef_search(q, 3, 100)
+    np.testing.assert_array_equal(keys, want["keys"])
+    np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32))
+
+
+def test_m0_smaller_than_m_is_clamped_not_overrun():
+    # the reference writes M links into a level-0 list sized M0 (out of bounds); gvss clamps to M0
+    base, q = synth.clustered(400, 6, 8, 3, 22, 20)
+    ix = gv.Index(6, "l2sq", M=6, M0=3, ef_construction=40)
+    ix.reserve(400, 1)
+    ix.add_batch(base)
+    ix.flush()
+    st = ix.stats(0)
+    assert st["nodes"] == 400 and st["edges"] <= 400 * 3
+    keys, dist, counts = ix.ef_search(base[:20], 1, 64)
+    assert (counts == 1).all() and (dist[:, 0] >= 0).all()
+
+
+def test_duplicate_vectors_and_removed_entry_point(checker):
+    Checker, _ = checker
+    base, q = synth.clustered(600, 8, 6, 3, 23, 30)
+    base[100:200] = base[0:100]                      # exact duplicates: distance-0 ties between nodes
+    ref = Checker(8, "l2sq")
+    ref.reserve(600, 1)
+    ref.add_bulk(base, threads=1)
+    ix = gv.Index(8, "l2sq")
+    ix.load(ref.save())
+    for ef in (10, 64):
+        want = ref.search_batch(q, 10, ef)
+        keys, dist, _ = ix.ef_search(q, 10, ef)
+        np.testing.assert_array_equal(keys, want["keys"])
+        np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32))
+    # remove the entry point itself: it is still traversed, only withheld from the results (index.hpp:3529-3533)
+    blob = ref.save()
+    off = 8 + 600 * 8 * 4 + 64
+    entry = int.from_bytes(blob[off + 32:off + 40], "little")
+    assert ref.remove(entry) == 1 and ix.remove(entry) == 1
+    want = ref.search_batch(q, 10, 64)
+    keys, dist, _ = ix.ef_search(q, 10, 64)
+    np.testing.assert_array_equal(keys, want["keys"])
+    assert not (keys == entry).any()
