@@ -112,6 +112,47 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
     return nkept;
 }
 
+// One directed link update under the target's lock: append `nbr` to `target`'s list on `level`, or, when the list is
+// full, re-run the heuristic over {(d_tn, nbr)} ∪ {(d(target, x), x)} with needed = capacity
+// (reconnect_neighbor_nodes_, index.hpp:3279-3311). `d_tn` = d(target, nbr).
+template <int METRIC>
+__device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t *locks, uint32_t target, uint32_t nbr, float d_tn,
+                                         int level, uint32_t *kept_s, float *kept_d, uint32_t top_limit_all, uint32_t &staged) {
+    const uint32_t lane = lane_id();
+    uint32_t capc;
+    uint32_t *clist = list_ptr(g, target, level, capc);
+    lock_node(locks, target);
+    uint32_t cntc = 0;
+    bool present = false;
+    for (uint32_t base = 0; base < capc; base += 32) {
+        const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
+        cntc += __popc(__ballot_sync(kFull, e != kInvalid));
+        present |= __ballot_sync(kFull, e == nbr) != 0;
+    }
+    if (present) { unlock_node(locks, target); return; }
+    if (cntc < capc) {
+        if (lane == 0) clist[cntc] = nbr;
+        unlock_node(locks, target);
+        return;
+    }
+    uint32_t tsz = 0;
+    top_insert(w, tsz, top_limit_all, d_tn, nbr);
+    for (uint32_t base = 0; base < capc; base += 32) {
+        const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
+        const bool act = e != kInvalid;
+        const uint32_t am = __ballot_sync(kFull, act);
+        if (!am) break;
+        const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, target}, e, act, staged);
+        for (uint32_t m = am; m; m &= m - 1) {
+            const uint32_t j = __ffs(m) - 1;
+            top_insert(w, tsz, top_limit_all, __shfl_sync(kFull, d, j), __shfl_sync(kFull, e, j));
+        }
+    }
+    const uint32_t nk2 = refine<METRIC>(g, w, tsz, capc, kept_s, kept_d, staged);
+    for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
+    unlock_node(locks, target);
+}
+
 template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     WarpWs w;
@@ -121,6 +162,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
     uint32_t *mine_s = reinterpret_cast<uint32_t *>(smem + p.sm.off_misc);
     uint32_t *kept_s = mine_s + (cmax + 1);
     float *kept_d = reinterpret_cast<float *>(kept_s + (cmax + 1));
+    float *mine_d = kept_d + (cmax + 1);
     const uint32_t top_limit_all = p.sm.top_cap; // never reached: plain insert_reserved
     uint32_t staged = kInvalid;
 
@@ -133,6 +175,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         const int level = p.levels[slot];
 
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = g.vectors[(size_t)slot * g.dpad + i];
+        if (p.inflight && lane == 0) __stcg(p.inflight + blockIdx.x, slot);
         __syncwarp();
 
         unsigned long long es = 0;
@@ -145,7 +188,10 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             }
         }
         es = __shfl_sync(kFull, es, 0);
-        if (es == ~0ull) continue;
+        if (es == ~0ull) { // this node became the first node of the graph
+            if (p.inflight && lane == 0) __stcg(p.inflight + blockIdx.x, kInvalid);
+            continue;
+        }
         const int max_level = (int)(es >> 32);
         const uint32_t entry = (uint32_t)(es & 0xFFFFFFFFull);
 
@@ -171,7 +217,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             uint32_t nk = refine<METRIC>(g, w, top_size, g.M, kept_s, kept_d, staged);
             nk = min(nk, cap_l);
             t_refine += clock64() - t0; t0 = clock64();
-            for (uint32_t i = lane; i < nk; i += 32) mine_s[i] = kept_s[i];
+            for (uint32_t i = lane; i < nk; i += 32) { mine_s[i] = kept_s[i]; mine_d[i] = kept_d[i]; }
             __syncwarp();
             uint32_t capx;
             uint32_t *mylist = list_ptr(g, slot, l, capx);
@@ -194,47 +240,49 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             t_conn += clock64() - t0; t0 = clock64();
 
             // reconnect_neighbor_nodes_
+            const float a_worst = nk ? kept_d[nk - 1] : CUDART_INF_F; // distance of this node's farthest own link
             for (uint32_t i = 0; i < nk; i++) {
                 const uint32_t close = mine_s[i];
                 if (close == slot) continue;
-                uint32_t capc;
-                uint32_t *clist = list_ptr(g, close, l, capc);
-                lock_node(p.locks, close);
-                uint32_t cntc = 0;
-                bool present = false;
-                for (uint32_t base = 0; base < capc; base += 32) {
-                    const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
-                    cntc += __popc(__ballot_sync(kFull, e != kInvalid));
-                    present |= __ballot_sync(kFull, e == slot) != 0;
-                }
-                if (present) { unlock_node(p.locks, close); continue; }
-                if (cntc < capc) {
-                    if (lane == 0) clist[cntc] = slot;
-                    unlock_node(p.locks, close);
-                    continue;
-                }
-                // saturated: candidates = {(d(new, close), new)} ∪ {(d(close, x), x)}, then the heuristic with needed = cap
-                uint32_t tsz = 0;
                 float dn = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
                 dn = __shfl_sync(kFull, dn, 0);
-                top_insert(w, tsz, top_limit_all, dn, slot);
-                for (uint32_t base = 0; base < capc; base += 32) {
-                    const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
-                    const bool act = e != kInvalid;
-                    const uint32_t am = __ballot_sync(kFull, act);
-                    if (!am) break;
-                    const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, close}, e, act, staged);
-                    for (uint32_t m = am; m; m &= m - 1) {
-                        const uint32_t j = __ffs(m) - 1;
-                        top_insert(w, tsz, top_limit_all, __shfl_sync(kFull, d, j), __shfl_sync(kFull, e, j));
+                add_link<METRIC>(g, w, p.locks, close, slot, dn, l, kept_s, kept_d, top_limit_all, staged);
+            }
+            // Inserts that are in flight at the same time cannot find each other through the graph. Before this node
+            // leaves, it measures its distance to every vector other warps are inserting right now and links both ways with
+            // those that are closer than its farthest own link (same append / re-prune rule as any reverse link). With one
+            // insert in flight the list is empty and the build stays byte-identical to the reference's single-thread build.
+            if (l == 0 && p.inflight && gridDim.x > 1) {
+                for (uint32_t base = 0; base < gridDim.x; base += 32) {
+                    const uint32_t wi = base + lane;
+                    const uint32_t x = wi < gridDim.x ? __ldcg(p.inflight + wi) : kInvalid;
+                    const bool act = x != kInvalid && x != slot && x < g.count;
+                    if (!__ballot_sync(kFull, act)) continue;
+                    const float d = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, x, act, staged);
+                    uint32_t cm = __ballot_sync(kFull, act && d < a_worst);
+                    while (cm) {
+                        const uint32_t j = __ffs(cm) - 1;
+                        cm &= cm - 1;
+                        const uint32_t xs = __shfl_sync(kFull, x, j);
+                        const float dx = __shfl_sync(kFull, d, j);
+                        // the heuristic's own test for a candidate at distance dx: dropped if one of this node's links that
+                        // is at least as close dominates it (refine_, index.hpp:3617-3627)
+                        bool dominated = false;
+                        for (uint32_t b2 = 0; b2 < nk; b2 += 32) {
+                            const bool a2 = b2 + lane < nk && mine_d[b2 + lane] <= dx;
+                            if (!__ballot_sync(kFull, a2)) continue;
+                            const float dxs = warp_distances<METRIC>(g, w, LeftSrc{nullptr, xs}, a2 ? mine_s[b2 + lane] : kInvalid, a2, staged);
+                            dominated |= __ballot_sync(kFull, a2 && dxs < dx) != 0u;
+                        }
+                        if (dominated) continue;
+                        add_link<METRIC>(g, w, p.locks, xs, slot, dx, 0, kept_s, kept_d, top_limit_all, staged);
+                        add_link<METRIC>(g, w, p.locks, slot, xs, dx, 0, kept_s, kept_d, top_limit_all, staged);
                     }
                 }
-                const uint32_t nk2 = refine<METRIC>(g, w, tsz, capc, kept_s, kept_d, staged);
-                for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
-                unlock_node(p.locks, close);
             }
             t_recon += clock64() - t0;
         }
+        if (p.inflight && lane == 0) __stcg(p.inflight + blockIdx.x, kInvalid);
         if (p.prof && lane == 0) {
             atomicAdd(p.prof + 0, (unsigned long long)t_greedy); atomicAdd(p.prof + 1, (unsigned long long)t_beam);
             atomicAdd(p.prof + 2, (unsigned long long)t_refine); atomicAdd(p.prof + 3, (unsigned long long)t_conn);

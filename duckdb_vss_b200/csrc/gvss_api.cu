@@ -881,15 +881,22 @@ static int flush_locked(gvss_index *x) {
     unsigned long long *d_prof = nullptr;
     if (prof_on) { CU(cudaMalloc(&d_prof, 64)); CU(cudaMemsetAsync(d_prof, 0, 64, x->stream)); }
     p.prof = d_prof;
+    // in-flight registry for the peer pass of k_build (GVSS_BUILD_PEERS=0 disables it)
+    static const bool peers_on = [] { const char *e = getenv("GVSS_BUILD_PEERS"); return e ? atoi(e) != 0 : true; }();
+    uint32_t *d_inflight = nullptr;
+    if (peers_on) {
+        CU(cudaMalloc(&d_inflight, (size_t)max_warps * 4));
+        CU(cudaMemsetAsync(d_inflight, 0xFF, (size_t)max_warps * 4, x->stream));
+    }
+    p.inflight = d_inflight;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
     if (prof_on) { cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventCreate(&ev2); cudaEventRecord(ev0, x->stream); }
     uint64_t linked = x->count - 0; // nodes already in the graph
-    // In-flight inserts are capped at (linked nodes / ramp). Vectors inserted at the same time cannot see each other, so
-    // small graphs need a strict cap (1/256: recall within 0.005 of a sequential build at 30k vectors), while in a large
-    // build the ramp region is a small, later repaired part of the graph and 1/64 costs nothing measurable at 1M
-    // (profiles/build_ramp_r1.txt). GVSS_BUILD_RAMP overrides.
-    const uint64_t final_nodes = x->count + slots.size();
-    uint64_t ramp = std::min<uint64_t>(256, std::max<uint64_t>(64, 25600000ull / std::max<uint64_t>(final_nodes, 1)));
+    // In-flight inserts are capped at (linked nodes / ramp). Vectors inserted at the same time cannot see each other through
+    // the graph; k_build's peer pass links them explicitly, which makes the cap almost irrelevant for quality (recall equal to
+    // the reference-built graph from ramp 2 to 256 at 30k and 1M vectors, profiles/build_ramp_r1.txt). 4 keeps the very first
+    // launches small. GVSS_BUILD_RAMP overrides.
+    uint64_t ramp = 4;
     if (const char *e = getenv("GVSS_BUILD_RAMP")) ramp = std::max<uint64_t>(1, strtoull(e, nullptr, 10));
     uint64_t done = 0;
     const uint64_t total = slots.size();
@@ -926,6 +933,7 @@ static int flush_locked(gvss_index *x) {
     CU(cudaMemcpyAsync(&es, x->d_entry_state, 8, cudaMemcpyDeviceToHost, x->stream));
     CU(cudaStreamSynchronize(x->stream));
     cudaFree(d_slots);
+    cudaFree(d_inflight);
     x->entry = (uint32_t)(es & 0xFFFFFFFFull);
     x->max_level = (int32_t)(es >> 32);
     x->count = next_fresh;
