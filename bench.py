@@ -356,6 +356,14 @@ def main():
     if rank == 0:
         peak, peak_src = peaks()
         achieved = algo_bytes / t_kernel / 1e9
+        traffic = None  # dram read+write bytes of one launch from the committed ncu --set full capture of this exact config
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_search_traffic.json")))
+            c = tj["config"]
+            if (c["n"], c["nq"], c["ef_search"], c["M"], c["dims"]) == (n, nq, ef, M, d):
+                traffic = tj["traffic_bytes_per_launch"]
+        except Exception:
+            traffic = None
         cpu = None
         if world == 1 and not args.no_cpu:
             cpu = cpu_baseline(args, ix.save, q_np, ef, truth_np, gpu_keys=kh.numpy())
@@ -373,7 +381,7 @@ def main():
                        "l2_policy": "inputs larger than L2: 512 MB vectors + 128 MB adjacency per GPU vs 126 MB L2; no flush",
                        "parallelism": f"shard{world}" if world > 1 else "single"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "k_search<l2sq>",
+                         "traffic": traffic, "peak_source": peak_src, "kernel": "k_search<l2sq>",
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": 1e3 * t_kernel},
             "cpu_baseline": cpu,
             "e2e": {"value": world * nq * args.steps / t_e2e, "unit": "queries/s", "h2d_bytes_per_step": h2d,
