@@ -72,6 +72,7 @@ struct gvss_index {
     uint64_t upper_cap = 0, upper_used = 0;      // in blocks of strideU u32
     uint8_t *d_scratch = nullptr;
     size_t scratch_bytes = 0;
+    cudaEvent_t scratch_free = nullptr; // recorded after every launch that uses the scratch / work counter
 
     // host mirrors
     std::vector<int64_t> h_keys;
@@ -165,6 +166,17 @@ static int16_t draw_level(uint64_t &state, uint32_t M) {
 
 static int flush_locked(gvss_index *x);
 
+// frees a temporary device allocation on every exit path (the CU() macro returns early)
+struct TempDev {
+    void *p = nullptr;
+    ~TempDev() { if (p) cudaFree(p); }
+    template <typename T> cudaError_t alloc(T *&out, size_t n) {
+        const cudaError_t e = cudaMalloc(&p, n ? n * sizeof(T) : sizeof(T));
+        out = static_cast<T *>(p);
+        return e;
+    }
+};
+
 // heap entries held in shared memory on the search path (GVSS_HEAP_SMEM overrides default_heap_smem for experiments)
 static uint32_t search_heap_smem(uint32_t limit) {
     static int v = [] { const char *e = getenv("GVSS_HEAP_SMEM"); return e ? atoi(e) : 0; }();
@@ -230,9 +242,13 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     if (ensure_scratch(x, p.sl.bytes_per_warp * grid)) return 1;
     p.scratch = x->d_scratch;
     p.work_counter = x->d_work;
+    // searches issued on different streams share the scratch and the work counter: order them on the device
+    if (!x->scratch_free) CU(cudaEventCreateWithFlags(&x->scratch_free, cudaEventDisableTiming));
+    else CU(cudaStreamWaitEvent(st, x->scratch_free, 0));
     CU(cudaMemsetAsync(x->d_work, 0, sizeof(unsigned long long), st));
     GraphView g = view_of(x);
     CU(launch_search(metric_id(x->cfg.metric), g, p, grid, st));
+    CU(cudaEventRecord(x->scratch_free, st));
     return 0;
 }
 
@@ -287,6 +303,7 @@ void gvss_destroy(gvss_index *x) {
     cudaFree(x->d_entry_state); cudaFree(x->d_work);
     cudaFree(x->d_q); cudaFree(x->d_ok); cudaFree(x->d_od); cudaFree(x->d_oc); cudaFree(x->d_os);
     if (x->h_pin) cudaFreeHost(x->h_pin);
+    if (x->scratch_free) cudaEventDestroy(x->scratch_free);
     if (x->stream) cudaStreamDestroy(x->stream);
     delete x;
 }
@@ -859,7 +876,8 @@ static int flush_locked(gvss_index *x) {
     // 3. graph construction: concurrency ramps with the graph size (a launch never runs more concurrent inserts than
     //    1/16 of the nodes already linked), then one persistent launch for the rest
     uint32_t *d_slots = nullptr;
-    CU(cudaMalloc(&d_slots, slots.size() * 4));
+    TempDev slots_mem, inflight_mem, prof_mem;
+    CU(slots_mem.alloc(d_slots, slots.size()));
     CU(cudaMemcpyAsync(d_slots, slots.data(), slots.size() * 4, cudaMemcpyHostToDevice, x->stream));
     BuildParams p{};
     p.slots = d_slots; p.levels = x->d_levels; p.entry_state = x->d_entry_state; p.work_counter = x->d_work; p.locks = x->d_locks;
@@ -872,20 +890,20 @@ static int flush_locked(gvss_index *x) {
     p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
-    if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) { cudaFree(d_slots); return 1; }
+    if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) return 1;
     p.scratch = x->d_scratch;
     unsigned long long es = x->max_level < 0 ? ~0ull : (((unsigned long long)(uint32_t)x->max_level << 32) | x->entry);
     CU(cudaMemcpyAsync(x->d_entry_state, &es, 8, cudaMemcpyHostToDevice, x->stream));
     // GVSS_BUILD_PROF=1: per-phase SM clocks summed over all inserts, and wall time of the ramp vs the final launch (stderr)
     static const bool prof_on = [] { const char *e = getenv("GVSS_BUILD_PROF"); return e && atoi(e); }();
     unsigned long long *d_prof = nullptr;
-    if (prof_on) { CU(cudaMalloc(&d_prof, 64)); CU(cudaMemsetAsync(d_prof, 0, 64, x->stream)); }
+    if (prof_on) { CU(prof_mem.alloc(d_prof, 8)); CU(cudaMemsetAsync(d_prof, 0, 64, x->stream)); }
     p.prof = d_prof;
     // in-flight registry for the peer pass of k_build (GVSS_BUILD_PEERS=0 disables it)
     static const bool peers_on = [] { const char *e = getenv("GVSS_BUILD_PEERS"); return e ? atoi(e) != 0 : true; }();
     uint32_t *d_inflight = nullptr;
     if (peers_on) {
-        CU(cudaMalloc(&d_inflight, (size_t)max_warps * 4));
+        CU(inflight_mem.alloc(d_inflight, max_warps));
         CU(cudaMemsetAsync(d_inflight, 0xFF, (size_t)max_warps * 4, x->stream));
     }
     p.inflight = d_inflight;
@@ -928,12 +946,10 @@ static int flush_locked(gvss_index *x) {
         const double n = h[5] ? (double)h[5] : 1.0;
         fprintf(stderr, "[gvss build] %llu inserts, %u warps max: total %.1f ms (final persistent launch %.1f ms); clocks/insert: greedy %.0f beam %.0f refine %.0f connect %.0f reconnect %.0f\n",
                 h[5], max_warps, ms_all, ms_last, h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n);
-        cudaFree(d_prof); cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
     }
     CU(cudaMemcpyAsync(&es, x->d_entry_state, 8, cudaMemcpyDeviceToHost, x->stream));
     CU(cudaStreamSynchronize(x->stream));
-    cudaFree(d_slots);
-    cudaFree(d_inflight);
     x->entry = (uint32_t)(es & 0xFFFFFFFFull);
     x->max_level = (int32_t)(es >> 32);
     x->count = next_fresh;
