@@ -429,6 +429,17 @@ static bool make_map(CUtensorMap *m, const float *ptr, uint64_t rows, uint32_t d
                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// k_search's gather4 staging: box = 32 floats (128 B) x 1 row; one instruction fetches that box from 4 arbitrary rows
+bool encode_row_gather_map(CUtensorMap *m, const float *vectors, uint64_t rows, uint32_t dpad) {
+    encode_tiled_fn enc = get_encode();
+    if (!enc || dpad < 32 || rows == 0) return false;
+    const cuuint64_t dims[2] = {dpad, rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)dpad * 4};
+    const cuuint32_t box[2] = {32, 1};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)vectors, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 struct DevBuf {
     void *p = nullptr;
     cudaStream_t st;

@@ -122,7 +122,7 @@ static void free_device(gvss_index *x) {
 
 static int ensure_capacity(gvss_index *x, uint64_t members) {
     if (members <= x->capacity) return 0;
-    if (members >= 0xFFFFFFF0ull) return fail("gvss: more than 2^32-16 members are not addressable with u32 slots");
+    if (members >= 0x7FFFFFF0ull) return fail("gvss: more than 2^31-16 members are not addressable (u32 slots, top bit reserved)");
     const uint64_t oldc = x->capacity;
     CU(dev_resize(x->d_vectors, oldc * x->dpad, members * x->dpad, 0, x->stream));
     CU(dev_resize(x->d_keys, oldc, members, 0, x->stream));
@@ -178,9 +178,13 @@ struct TempDev {
 };
 
 // heap entries held in shared memory on the search path (GVSS_HEAP_SMEM overrides default_heap_smem for experiments)
-static uint32_t search_heap_smem(uint32_t limit) {
-    static int v = [] { const char *e = getenv("GVSS_HEAP_SMEM"); return e ? atoi(e) : 0; }();
-    return v > 0 ? (uint32_t)v : default_heap_smem(limit);
+// With the list-as-queue search (no removed members) the heap only serves the rare exact-tie replay and lives in global
+// scratch entirely: the 2 KB it would take per query buy more resident queries.
+static bool list_queue();
+static uint32_t search_heap_smem(const gvss_index *x, uint32_t limit) {
+    static int v = [] { const char *e = getenv("GVSS_HEAP_SMEM"); return e ? atoi(e) : -1; }();
+    if (v >= 0) return (uint32_t)v / 32u * 32u;
+    return (list_queue() && !x->n_deleted) ? 0u : default_heap_smem(limit);
 }
 // rows of the staging buffer on the search path: 16 halves the shared memory per query (more resident warps); 32 serves
 // a whole 32-neighbour batch in one go. GVSS_STAGE_ROWS overrides for experiments.
@@ -199,6 +203,10 @@ static uint32_t search_stage_chunk() {
 }
 // query-to-node distances: 0 = rows staged in shared memory by TMA bulk copies (default: faster once the base set
 // exceeds L2, profiles/r1_search_ncu_summary.txt), 1 = rows streamed straight into registers (256-bit loads, no staging). GVSS_DIRECT_ROWS overrides for A/B measurements.
+static bool list_queue() { // GVSS_LIST_QUEUE=0: k_search always replays usearch's heap (A/B, debugging)
+    static bool on = [] { const char *e = getenv("GVSS_LIST_QUEUE"); return e ? atoi(e) != 0 : true; }();
+    return on;
+}
 static bool direct_rows() {
     static bool on = [] { const char *e = getenv("GVSS_DIRECT_ROWS"); return GVSS_DIRECT_PATH && e ? atoi(e) != 0 : false; }();
     return on;
@@ -217,6 +225,21 @@ static bool spec_prefetch() {
 // ------------------------------------------------------------------------------------------------------------
 // search
 // ------------------------------------------------------------------------------------------------------------
+static bool gather4_rows() { // GVSS_GATHER4=0: stage rows with one 1-D bulk copy per row chunk instead of TMA gather4
+    static bool on = [] { const char *e = getenv("GVSS_GATHER4"); return e ? atoi(e) != 0 : true; }();
+    return on;
+}
+static int search_mode_bits() {
+    return (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4) | (list_queue() ? 0 : 8);
+}
+// gather4 staging needs rows of at least one 128-byte line and a tensor map over the vector array
+static bool setup_gather4(const gvss_index *x, SearchParams &p) {
+    if (!gather4_rows() || direct_rows() || !stage_with_tma() || x->dpad < 32 || !x->capacity) return false;
+    if (!encode_row_gather_map(&p.vmap, x->d_vectors, x->capacity, x->dpad)) return false;
+    p.direct |= 16;
+    return true;
+}
+
 static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t nq, uint32_t k, uint32_t ef,
                                 int64_t *d_keys_out, float *d_dist_out, uint32_t *d_counts_out,
                                 gvss_search_stats *d_stats_out, cudaStream_t st) {
@@ -232,8 +255,9 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false);
-    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
+    p.direct = search_mode_bits();
+    const bool g4 = setup_gather4(x, p);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false, g4);
     uint32_t grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
     static const uint32_t max_warps = [] { const char *e = getenv("GVSS_SEARCH_MAX_WARPS"); return e ? (uint32_t)atoi(e) : 0u; }();
@@ -456,8 +480,9 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     p.trace_query = -1;
     p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false);
-    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
+    p.direct = search_mode_bits();
+    const bool g4 = setup_gather4(x, p);
+    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false, g4);
     const uint32_t resident = resident_warps(x->device, p.sm.bytes, false);
     if (!resident) return fail("gvss: no CUDA device");
     char err[384];
@@ -887,7 +912,7 @@ static int flush_locked(gvss_index *x) {
     p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
     static const uint32_t build_rows = [] { const char *e = getenv("GVSS_BUILD_STAGE_ROWS"); const uint32_t v = e ? (uint32_t)atoi(e) : 32u; return v == 16u ? 16u : 32u; }();
     p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, build_rows, true, cmax);
-    p.direct = (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4);
+    p.direct = search_mode_bits();
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
     if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) return 1;

@@ -12,6 +12,7 @@
 // :3504-3573 search_to_find_in_base_, :3430-3496 search_to_insert_), so results, their order among ties and the
 // traversal counters are identical to the reference on the same graph.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <math_constants.h>
 #include <stdint.h>
@@ -62,6 +63,8 @@ struct WarpWs {
     bool use_tma;        // rows staged by TMA bulk copies (cp.async.bulk) or by coalesced 16-byte cp.async
     bool spec_prefetch;  // prefetch every neighbour's row to L2 before the visited test resolves (trades HBM traffic for latency)
     bool direct;         // query-to-node distances stream each lane's row straight into registers (no staging)
+    bool g4;             // query-to-node distances stage 32 rows x 32 floats per step by TMA gather4 (stage[0]: 4 KB, 1024-aligned)
+    const CUtensorMap *vmap; // ... through this 2-D map over `vectors`
     uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
     float *nd;           // ... and their distances
     float *top_d;        // result list, ascending
@@ -82,6 +85,20 @@ struct Counters {
     uint32_t computed, cycles, base;
     uint32_t flags; // bit0: visited table / queue overflow; bit31: trace this query (debug aid, GVSS_TRACE_QUERY)
 };
+
+// Operation counts for kernel tuning (build with -DGVSS_OPCOUNT=1; read with the debug hook gvssdbg_opcounts). Off in the
+// shipped library: OPC() compiles to nothing.
+#ifndef GVSS_OPCOUNT
+#define GVSS_OPCOUNT 0
+#endif
+#if GVSS_OPCOUNT
+enum { kOpQueries, kOpHops, kOpNew, kOpHopsLe16, kOpHopsNone, kOpPushes, kOpPrunes, kOpPruneKept, kOpInsBatches, kOpInserted,
+       kOpShifted, kOpVisRounds, kOpMaybeBatches, kOpPushLevels, kOpPopLevels, kOpCount };
+static __device__ unsigned long long g_opcount[kOpCount];
+#define OPC(i, v) do { if (lane_id() == 0) atomicAdd(&g_opcount[i], (unsigned long long)(v)); } while (0)
+#else
+#define OPC(i, v) do { } while (0)
+#endif
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -115,6 +132,17 @@ __device__ __forceinline__ void tma_row(void *dst, const void *src, uint32_t byt
                      smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
+}
+// TMA gather: the same 128-byte column window [col, col+32) of FOUR arbitrary rows of a 2-D tensor in one instruction
+// (SASS UTMALDG...GATHER4); the rows land 128 B apart, 16-byte granules XOR-swizzled with the row index (SWIZZLE_128B).
+// A row index outside the tensor reads as zeros without touching memory.
+__device__ __forceinline__ void tma_gather4(void *dst, const CUtensorMap *map, int col, int r0, int r1, int r2, int r3,
+                                            uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(col), "r"(r0), "r"(r1), "r"(r2), "r"(r3)
+        : "memory");
 }
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
@@ -225,6 +253,57 @@ __device__ __noinline__ float direct_distance(const float *vectors, uint32_t dpa
     return acc_finish<METRIC>(acc);
 }
 
+// Query-to-node distances with gather4 staging: lane i <-> row i for all 32 lanes, 32 floats (one 128-byte line) of every
+// row per step. Lane 4j issues the copy for lanes 4j..4j+3 (inactive lanes name a row outside the tensor: zero fill, no
+// traffic). Reads are conflict-free: in each 8-lane phase of an LDS.128 the swizzle spreads the lanes over all 8 granules.
+constexpr int kG4Chunk = 32;
+constexpr int kG4OobRow = 0x7FFFFFFF;
+template <int METRIC>
+__device__ __forceinline__ float warp_distances_g4(const GraphView &g, WarpWs &w, uint32_t my_slot, bool active) {
+    const uint32_t lane = lane_id();
+    const uint32_t amask = __ballot_sync(kFull, active);
+    if (!amask) return 0.0f;
+    // groups of 4 lanes with at least one active lane
+    uint32_t gm = amask | (amask >> 1);
+    gm = (gm | (gm >> 2)) & 0x11111111u;
+    const uint32_t ngroups = __popc(gm);
+    const int r0 = active ? (int)my_slot : kG4OobRow;
+    const int r1 = __shfl_down_sync(kFull, r0, 1), r2 = __shfl_down_sync(kFull, r0, 2), r3 = __shfl_down_sync(kFull, r0, 3);
+    const bool issuer = (gm >> lane) & 1u;
+    float *sbuf = w.stage[0];
+    const uint32_t nchunks = (g.dpad + kG4Chunk - 1) / kG4Chunk;
+    const float4 *myrow = reinterpret_cast<const float4 *>(sbuf + lane * kG4Chunk);
+    const uint32_t sw = lane & 7u;
+    Acc acc = {0.0f, 0.0f, 0.0f};
+    for (uint32_t ch = 0; ch < nchunks; ch++) {
+        if (lane == 0) mbar_expect_tx(w.mbar, ngroups * 4u * kG4Chunk * 4u);
+        __syncwarp();
+        if (issuer) tma_gather4(sbuf + lane * kG4Chunk, w.vmap, (int)(ch * kG4Chunk), r0, r1, r2, r3, w.mbar);
+        mbar_wait(w.mbar, w.phase[0]);
+        w.phase[0] ^= 1u;
+        if (active) {
+            const uint32_t nfl = min((uint32_t)kG4Chunk, g.dpad - ch * kG4Chunk);
+            const float4 *a = reinterpret_cast<const float4 *>(w.q + ch * kG4Chunk);
+            if (nfl == kG4Chunk) {
+#pragma unroll
+                for (uint32_t i = 0; i < kG4Chunk / 4; i++) {
+                    const float4 x = a[i], y = myrow[i ^ sw];
+                    acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
+                    acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                }
+            } else {
+                for (uint32_t i = 0; i < nfl / 4; i++) {
+                    const float4 x = a[i], y = myrow[i ^ sw];
+                    acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
+                    acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                }
+            }
+        }
+        __syncwarp(); // all lanes are done reading the buffer before it is refilled
+    }
+    return active ? acc_finish<METRIC>(acc) : 0.0f;
+}
+
 // Where the left-hand vector of a distance batch comes from.
 struct LeftSrc {
     const float *smem; // whole row resident in shared memory (the query), or nullptr
@@ -244,6 +323,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
+    if (w.g4 && !stream_left) return warp_distances_g4<METRIC>(g, w, my_slot, active);
 #if GVSS_DIRECT_PATH
     if (w.direct && !stream_left) { // no staging at all: all 32 lanes at once
         const float d = direct_distance<METRIC>(g.vectors, g.dpad, left.smem, my_slot, active);
@@ -385,6 +465,7 @@ __device__ __forceinline__ bool vis_insert_warp(WarpWs &w, uint32_t key, bool wa
     uint32_t base = ((key * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1);
     bool pending = want, isnew = false;
     while (__ballot_sync(kFull, pending)) {
+        OPC(kOpVisRounds, 1);
         uint4 a = make_uint4(0u, 0u, 0u, 0u), b = a;
         if (pending) {
             a = __ldcg(reinterpret_cast<const uint4 *>(w.vis + base));
@@ -477,6 +558,7 @@ __device__ __forceinline__ bool heap_push(WarpWs &w, uint32_t &size, float d, ui
             if (!(pe.d > d)) break; // less(parent, child) on negated distances
             heap_set(w, i, pe);
             i = p;
+            OPC(kOpPushLevels, 1);
         }
         heap_set(w, i, Cand{d, s});
     }
@@ -499,6 +581,7 @@ __device__ __forceinline__ void heap_pop(WarpWs &w, uint32_t &size) {
             if (mx == i) break;
             heap_set(w, i, mx == l ? le : re);
             i = mx;
+            OPC(kOpPopLevels, 1);
         }
         heap_set(w, i, x);
     }
@@ -618,13 +701,26 @@ __device__ __forceinline__ uint32_t top_upper_bound(const float *td, uint32_t n,
 //   * the new result list is the merge of the old one with the accepted allowed candidates, an element equal to
 //     existing ones going BEFORE them and later candidates before earlier equal ones (sorted_buffer_gt::insert uses
 //     lower_bound), cut at `limit`.
-template <int METRIC, bool INSERT, bool VOLATILE>
+//
+// LQ = true ("list as queue"): every candidate the reference can still pop is an unexpanded member of the result list
+// (an entry that fell off the list lies above the radius for good), and as long as no two such candidates have EQUAL
+// distances the heap pops them in ascending distance — i.e. in list order. The queue is then not materialised at all:
+// expanded members carry a flag in the top bit of their slot and the next candidate is the first unflagged entry. A
+// candidate that ties with a list member or with another candidate of its batch sets flag bit2 and ends the search; the
+// caller repeats it with the real heap (LQ = false), which keeps usearch's pop order among ties. Not used when the index
+// holds removed members (they enter the queue but not the list).
+constexpr uint32_t kExpanded = 0x80000000u;
+constexpr uint32_t kSlotMask = 0x7FFFFFFFu;
+
+template <int METRIC, bool INSERT, bool VOLATILE, bool LQ = false>
 __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, uint32_t limit, int level,
                                             uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged) {
     const uint32_t lane = lane_id();
     const uint32_t lt_mask = (1u << lane) - 1u;
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
+    uint32_t scan_from = 0; // LQ: every list entry before this index is expanded
+    float ghost = CUDART_INF_F; // LQ: smallest distance among the live entries that fell off the list (still in the reference's queue)
     top_size = 0;
     vis_clear(w);
 
@@ -632,7 +728,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     radius = __shfl_sync(kFull, radius, 0);
     if (radius != radius) radius = CUDART_INF_F;
     cnt.computed++;
-    heap_push(w, heap_size, radius, start);
+    if constexpr (!LQ) heap_push(w, heap_size, radius, start);
     if (lane == 0) vis_insert(w, start);
     const bool start_ok = INSERT || !g.has_deleted || __ldg(&g.keys[start]) != INT64_MAX;
     if (start_ok) {
@@ -643,19 +739,60 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     }
     __syncwarp();
 
-    while (heap_size) {
-        const Cand c = heap_get(w, 0);
-        if (INSERT) { if (c.d > radius && top_size == limit) break; }
-        else if (c.d > radius) break;
-        heap_pop(w, heap_size);
+    for (;;) {
+        Cand c;
+        uint32_t next_slot = kInvalid; // most likely next candidate (prefetch hint)
+        if constexpr (LQ) {
+            uint32_t cur = top_size, nxt = top_size;
+            bool later = false; // the next unexpanded entry (if any) lies beyond the window that holds `cur`
+            for (uint32_t i0 = scan_from & ~31u; i0 < top_size; i0 += 32) {
+                const uint32_t i = i0 + lane;
+                const bool un = i >= scan_from && i < top_size && !(w.top_s[i] & kExpanded);
+                const uint32_t um = __ballot_sync(kFull, un);
+                if (um) {
+                    cur = i0 + (uint32_t)__ffs(um) - 1u;
+                    const uint32_t um2 = um & (um - 1u);
+                    if (um2) nxt = i0 + (uint32_t)__ffs(um2) - 1u;
+                    else { nxt = i0 + 32u; later = true; }
+                    break;
+                }
+            }
+            if (cur >= top_size) {
+                // nothing left to expand: the reference's queue is empty or its head fell off the list earlier, i.e. lies
+                // above the radius and ends the search — unless it EQUALS the radius, then the reference expands it
+                if (top_size == limit && ghost == radius) cnt.flags |= 4u;
+                break;
+            }
+            c.d = w.top_d[cur];
+            c.s = w.top_s[cur] & kSlotMask;
+            if (c.d == ghost) { cnt.flags |= 4u; return; } // an entry outside the list ties with the queue head
+            if (nxt < top_size) {
+                // two live candidates at the same distance: the reference's pop order depends on its heap's history
+                // (`later`: conservative, the equal entry may already be expanded)
+                if (w.top_d[nxt] == c.d) { cnt.flags |= 4u; return; }
+                if (!later) next_slot = w.top_s[nxt] & kSlotMask;
+            }
+            __syncwarp();
+            if (lane == 0) w.top_s[cur] = c.s | kExpanded;
+            __syncwarp();
+            scan_from = cur + 1;
+        } else {
+            if (!heap_size) break;
+            c = heap_get(w, 0);
+            if (INSERT) { if (c.d > radius && top_size == limit) break; }
+            else if (c.d > radius) break;
+            heap_pop(w, heap_size);
+            if (heap_size) next_slot = heap_get(w, 0).s;
+        }
         cnt.cycles++;
         cnt.base++;
+        OPC(kOpHops, 1);
         if ((cnt.flags & 0x80000000u) && lane == 0)
             printf("pop %u slot %u d %.9g radius %.9g heap %u top %u computed %u\n", cnt.base, c.s, c.d, radius, heap_size, top_size, cnt.computed);
         if (INSERT && c.s == new_slot) continue;
-        if (heap_size) { // the next candidate is most likely the current queue head: pull its adjacency row towards L2
+        if (next_slot != kInvalid) { // pull its adjacency row towards L2
             uint32_t pcap;
-            const uint32_t *plist = list_ptr(g, heap_get(w, 0).s, level, pcap);
+            const uint32_t *plist = list_ptr(g, next_slot, level, pcap);
             if (lane * 32 < pcap) prefetch_l2(plist + lane * 32);
         }
 
@@ -683,11 +820,14 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             nvis += __popc(nmask);
         }
         __syncwarp();
+        OPC(kOpNew, nnew);
+        if (nnew <= 16) OPC(kOpHopsLe16, 1);
+        if (!nnew) OPC(kOpHopsNone, 1);
         if (!nnew) continue;
         cnt.computed += nnew;
 
         // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
-        const uint32_t bw = (GVSS_DIRECT_PATH && w.direct) ? 32u : w.stage_rows; // rows per distance batch
+        const uint32_t bw = ((GVSS_DIRECT_PATH && w.direct) || w.g4) ? 32u : w.stage_rows; // rows per distance batch
         for (uint32_t i = bw * 4 + lane; i < nnew * 4; i += 32) {
             const uint32_t lines = (g.dpad * 4 + 127) / 128;
             if ((i & 3u) < lines) prefetch_l2(g.vectors + (size_t)w.nb[i >> 2] * g.dpad + (i & 3u) * 32);
@@ -711,6 +851,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             // acceptance of a later one (the radius only shrinks), so the group is thinned before any bookkeeping
             const bool maybe = have && (top_size < limit || dj < radius);
             if (!__ballot_sync(kFull, maybe)) continue;
+            OPC(kOpMaybeBatches, 1);
             const bool allowed = maybe && (INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX);
             const uint32_t amask = __ballot_sync(kFull, allowed);
             // list size and order statistic as the reference would see them just before candidate j
@@ -726,10 +867,13 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const uint32_t accmask = __ballot_sync(kFull, acc);
             if (!accmask) continue;
 
-            for (uint32_t m = accmask; m; m &= m - 1) { // next.insert in list order
-                const uint32_t i = __ffs(m) - 1;
-                if (heap_size == w.heap_smem && top_size == limit) heap_prune(w, heap_size, radius);
-                if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
+            OPC(kOpPushes, __popc(accmask));
+            if constexpr (!LQ) {
+                for (uint32_t m = accmask; m; m &= m - 1) { // next.insert in list order
+                    const uint32_t i = __ffs(m) - 1;
+                    if (w.heap_smem && heap_size == w.heap_smem && top_size == limit) heap_prune(w, heap_size, radius);
+                    if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
+                }
             }
 
             const bool ins = acc && allowed;
@@ -743,7 +887,19 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     const float di = __shfl_sync(kFull, dj, i);
                     before += (di < dj || (di == dj && i > lane)) ? 1u : 0u;
                 }
+                // LQ: smallest distance among the live entries this update pushes off the list (they stay in the
+                // reference's queue; harmless there unless the queue head ever EQUALS one of them)
+                float dropped = CUDART_INF_F;
+                bool has_drop = false;
+                if constexpr (LQ) {
+                    const uint32_t at = (ins && lb + before < limit) ? lb + before : 0xFFFFFFFFu;
+                    scan_from = min(scan_from, __reduce_min_sync(kFull, at));
+                    if (ins && lb + before >= limit) { dropped = dj; has_drop = true; }
+                }
                 const uint32_t pmin = __reduce_min_sync(kFull, lb);
+                OPC(kOpInsBatches, 1);
+                OPC(kOpInserted, m_ins);
+                OPC(kOpShifted, top_size - pmin);
                 // old elements [pmin, top_size) move up by the number of insertions at or before them; windows from the top
                 for (int32_t hi = (int32_t)top_size; hi > (int32_t)pmin; hi -= 32) {
                     const int32_t i = hi - 1 - (int32_t)lane;
@@ -757,12 +913,24 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     }
                     __syncwarp();
                     if (mv && (uint32_t)i + sh < limit) { w.top_d[i + sh] = td; w.top_s[i + sh] = ts; }
+                    if constexpr (LQ) {
+                        if (mv && (uint32_t)i + sh >= limit && !(ts & kExpanded)) { dropped = fminf(dropped, td); has_drop = true; }
+                    }
                     __syncwarp();
                 }
                 if (ins && lb + before < limit) { w.top_d[lb + before] = dj; w.top_s[lb + before] = sj; }
                 top_size = min(limit, top_size + m_ins);
                 __syncwarp();
                 radius = w.top_d[top_size - 1];
+                if constexpr (LQ) {
+                    if (__ballot_sync(kFull, has_drop)) {
+                        uint32_t u = __float_as_uint(dropped); // order-preserving key for the warp-wide minimum
+                        u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+                        u = __reduce_min_sync(kFull, u);
+                        u = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
+                        ghost = fminf(ghost, __uint_as_float(u));
+                    }
+                }
             }
         }
     }

@@ -1,5 +1,6 @@
 // Host-visible launch interface of the CUDA kernels (internal to libgvss; the public boundary is include/gvss.h).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/gvss.h"
@@ -17,7 +18,9 @@ struct SmemLayout {
 // chunk: floats of a row staged per step (0 = default min(dpad, 128)); double_buffer: two stage buffers when a row spans
 // several chunks (build), else the chunks are staged one after the other into one buffer (search: half the footprint)
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap, uint32_t chunk = 0, bool double_buffer = true);
+                            bool with_left, uint32_t list_cap, uint32_t chunk = 0, bool double_buffer = true, bool gather4 = false);
+// tensor map for the gather4 staging path (exact_tc.cu holds the driver entry point); false when the driver refuses
+bool encode_row_gather_map(CUtensorMap *m, const float *vectors, uint64_t rows, uint32_t dpad);
 uint32_t default_heap_smem(uint32_t beam);
 
 // global scratch of one warp: visited table (vis_slots u32) followed by the queue overflow (heap_ovf Cand)
@@ -41,8 +44,11 @@ struct SearchParams {
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;
+    alignas(64) CUtensorMap vmap; // 2-D map over `vectors` ([capacity][dpad], box 32 floats x 1 row, 128-byte swizzle) for row gathers
     long long trace_query; // -1 = off
-    int direct;            // bit0: stream rows into registers instead of staging them; bit1: speculative row prefetch
+    int direct;            // bit0: stream rows into registers instead of staging them; bit1: speculative row prefetch;
+                           // bit2: stage with cp.async instead of TMA; bit3: always use usearch's heap as the queue;
+                           // bit4: rows staged by TMA gather4 (4 rows per instruction) through `vmap`, 32 rows x 32 floats per step
 };
 // grid = number of resident warps; returns cudaError
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);

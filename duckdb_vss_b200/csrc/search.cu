@@ -8,7 +8,9 @@
 namespace gvss {
 
 __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
-                                      const ScratchLayout &sl, int direct) {
+                                      const ScratchLayout &sl, int direct, const CUtensorMap *vmap) {
+    w.g4 = (direct & 16) != 0;
+    w.vmap = vmap;
     w.direct = (direct & 1) != 0;
     w.spec_prefetch = (direct & 2) != 0;
     w.use_tma = (direct & 4) == 0;
@@ -45,10 +47,13 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
     __syncwarp();
 }
 
-template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g, SearchParams p) {
-    extern __shared__ __align__(128) unsigned char smem[];
+#ifndef GVSS_SEARCH_MIN_BLOCKS
+#define GVSS_SEARCH_MIN_BLOCKS 24
+#endif
+template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOCKS) k_search(GraphView g, const __grid_constant__ SearchParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
     WarpWs w;
-    carve(w, smem, p.sm, p.scratch, p.sl, p.direct);
+    carve(w, smem, p.sm, p.scratch, p.sl, p.direct, &p.vmap);
     const uint32_t lane = lane_id();
     uint32_t staged = kInvalid;
 
@@ -64,22 +69,30 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
 
         Counters cnt = {0, 0, 0, (long long)qi == p.trace_query ? 0x80000000u : 0u};
         uint32_t top_size = 0;
+        OPC(kOpQueries, 1);
         if (g.count && p.k) {
             const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
             const Counters before = cnt;
-            beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
-            if (cnt.flags & 1u) { // the hashed visited table would have overfilled: redo the level with the exact bitmap
+            // fast path first (list as queue, hashed visited table); a query that would overfill the table is redone with
+            // the exact bitmap (flag bit1), one that meets an exact tie with usearch's heap as the queue (flag bit2)
+            const bool lq_ok = !g.has_deleted && (p.direct & 8) == 0;
+            bool lq = lq_ok, bitmap = false;
+            for (;;) {
                 cnt = before;
-                w.use_bitmap = true;
-                beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
-                w.use_bitmap = false;
-                cnt.flags |= 2u;
+                w.use_bitmap = bitmap;
+                if (lq) beam_search<METRIC, false, false, true>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
+                else beam_search<METRIC, false, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
+                if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
+                if (lq && (cnt.flags & 4u)) { lq = false; continue; }
+                break;
             }
+            w.use_bitmap = false;
+            cnt.flags = (cnt.flags & ~6u) | (bitmap ? 2u : 0u) | (!lq && lq_ok ? 4u : 0u);
         }
         const uint32_t n = min(top_size, p.k); // top.shrink(wanted), index.hpp:2526-2527
         for (uint32_t i = lane; i < p.k; i += 32) {
             const bool have = i < n;
-            p.keys_out[qi * p.k + i] = have ? __ldg(&g.keys[w.top_s[i]]) : -1; // dump_to: slot -> key, index.hpp:2252-2258
+            p.keys_out[qi * p.k + i] = have ? __ldg(&g.keys[w.top_s[i] & kSlotMask]) : -1; // dump_to: slot -> key, index.hpp:2252-2258
             if (p.dist_out) p.dist_out[qi * p.k + i] = have ? w.top_d[i] : CUDART_INF_F;
         }
         if (lane == 0) {
@@ -91,20 +104,23 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_search(GraphView g
 }
 
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer) {
+                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer, bool gather4) {
     SmemLayout s{};
     if (chunk == 0 || chunk > (uint32_t)kChunk) chunk = (uint32_t)kChunk;
+    if (gather4) { chunk = kG4Chunk; stage_rows = 32; double_buffer = false; }
     const uint32_t chunkf = dpad < chunk ? dpad : chunk;
     s.chunk = chunkf;
     s.rstride = chunkf + (((chunkf / 4) % 2 == 0) ? 4u : 0u); // odd number of 16-byte granules per row
+    if (gather4) s.rstride = kG4Chunk;                         // dense 128-byte rows, conflicts removed by the TMA swizzle
     s.stage_rows = stage_rows;
     const uint32_t stage_bytes = stage_rows * s.rstride * 4u;
     const bool two = double_buffer && dpad > chunkf;
     s.nbuf = two ? 2u : 1u;
     uint32_t off = 0;
     auto take = [&](uint32_t bytes, uint32_t align) { off = (off + align - 1) / align * align; uint32_t o = off; off += bytes; return o; };
+    if (gather4) s.off_stage0 = take(stage_bytes, 1024); // swizzle atoms are 1024-byte aligned: first in the carve-out
     s.off_mbar = take(16, 16);
-    s.off_stage0 = take(stage_bytes, 128);
+    if (!gather4) s.off_stage0 = take(stage_bytes, 128);
     s.off_stage1 = two ? take(stage_bytes, 128) : s.off_stage0;
     s.off_c = take(with_left ? 2 * kChunk * 4 : 0, 128);
     s.off_q = take(dpad * 4, 16);
@@ -222,6 +238,18 @@ cudaError_t launch_search_static_scratch(int metric, int device, const GraphView
     if (e != cudaSuccess) snprintf(err, err_len, "gvss_search_device_noalloc: launch failed: %s", cudaGetErrorString(e));
     return e;
 }
+
+#if GVSS_OPCOUNT
+// debug hook (not part of the ABI): read and reset the operation counters of an OPCOUNT build
+extern "C" int gvssdbg_opcounts(unsigned long long *out, int n) {
+    unsigned long long h[kOpCount] = {};
+    if (cudaMemcpyFromSymbol(h, g_opcount, sizeof(h)) != cudaSuccess) return -1;
+    for (int i = 0; i < n && i < kOpCount; i++) out[i] = h[i];
+    unsigned long long z[kOpCount] = {};
+    cudaMemcpyToSymbol(g_opcount, z, sizeof(z));
+    return kOpCount;
+}
+#endif
 
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
     switch (metric) {
