@@ -17,6 +17,8 @@ __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, cons
                                             const ScratchLayout &sl, int direct) {
     w.g4 = false; // the build stages whole rows (neighbour selection re-reads them); gather4 staging is a search path
     w.vmap = nullptr;
+    w.prefetch_rows = false;
+    w.prefetch_vis = false;
     w.direct = (direct & 1) != 0;
     w.spec_prefetch = (direct & 2) != 0;
     w.use_tma = (direct & 4) == 0;

@@ -230,7 +230,9 @@ static bool gather4_rows() { // GVSS_GATHER4=0: stage rows with one 1-D bulk cop
     return on;
 }
 static int search_mode_bits() {
-    return (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4) | (list_queue() ? 0 : 8);
+    static const bool pf = [] { const char *e = getenv("GVSS_PREFETCH_ROWS"); return e ? atoi(e) != 0 : true; }();
+    static const bool pv = [] { const char *e = getenv("GVSS_PREFETCH_VIS"); return e ? atoi(e) != 0 : true; }();
+    return (direct_rows() ? 1 : 0) | (spec_prefetch() ? 2 : 0) | (stage_with_tma() ? 0 : 4) | (list_queue() ? 0 : 8) | (pf ? 0 : 32) | (pv ? 0 : 64);
 }
 // gather4 staging needs rows of at least one 128-byte line and a tensor map over the vector array
 static bool setup_gather4(const gvss_index *x, SearchParams &p) {

@@ -65,6 +65,8 @@ struct WarpWs {
     bool direct;         // query-to-node distances stream each lane's row straight into registers (no staging)
     bool g4;             // query-to-node distances stage 32 rows x 32 floats per step by TMA gather4 (stage[0]: 4 KB, 1024-aligned)
     const CUtensorMap *vmap; // ... through this 2-D map over `vectors`
+    bool prefetch_rows;  // g4: L2 prefetch of every line of every new row at the start of a hop
+    bool prefetch_vis;   // L2 prefetch of the visited windows of neighbours 32.. while neighbours 0..31 are tested
     uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
     float *nd;           // ... and their distances
     float *top_d;        // result list, ascending
@@ -800,6 +802,11 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         uint32_t cap;
         const uint32_t *list = list_ptr(g, c.s, level, cap);
         uint32_t nnew = 0;
+        if (w.prefetch_vis && !w.use_bitmap && cap > 32) {
+            // the visited windows of the second block of neighbours start their trip from DRAM while the first block is tested
+            const uint32_t s1 = 32 + lane < cap ? ld_adj<VOLATILE>(list + 32 + lane) : kInvalid;
+            if (s1 != kInvalid) prefetch_l2(w.vis + (((s1 * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1)));
+        }
         for (uint32_t base = 0; base < cap; base += 32) {
             const uint32_t idx = base + lane;
             const uint32_t s = idx < cap ? ld_adj<VOLATILE>(list + idx) : kInvalid;
@@ -828,9 +835,19 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
 
         // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
         const uint32_t bw = ((GVSS_DIRECT_PATH && w.direct) || w.g4) ? 32u : w.stage_rows; // rows per distance batch
-        for (uint32_t i = bw * 4 + lane; i < nnew * 4; i += 32) {
+        if (w.g4 && w.prefetch_rows) {
+            // gather4 staging takes one 128-byte line of every row per step: get ALL lines of all new rows moving towards L2
+            // now, so that only the first step of the hop waits for DRAM
             const uint32_t lines = (g.dpad * 4 + 127) / 128;
-            if ((i & 3u) < lines) prefetch_l2(g.vectors + (size_t)w.nb[i >> 2] * g.dpad + (i & 3u) * 32);
+            for (uint32_t i = lane; i < nnew * lines; i += 32) {
+                const uint32_t r = i / lines, l = i - r * lines;
+                if (r || l) prefetch_l2(g.vectors + (size_t)w.nb[r] * g.dpad + l * 32);
+            }
+        } else {
+            for (uint32_t i = bw * 4 + lane; i < nnew * 4; i += 32) {
+                const uint32_t lines = (g.dpad * 4 + 127) / 128;
+                if ((i & 3u) < lines) prefetch_l2(g.vectors + (size_t)w.nb[i >> 2] * g.dpad + (i & 3u) * 32);
+            }
         }
         for (uint32_t b = 0; b < nnew; b += bw) {
             const bool act = lane < bw && b + lane < nnew;

@@ -48,7 +48,8 @@ struct SearchParams {
     long long trace_query; // -1 = off
     int direct;            // bit0: stream rows into registers instead of staging them; bit1: speculative row prefetch;
                            // bit2: stage with cp.async instead of TMA; bit3: always use usearch's heap as the queue;
-                           // bit4: rows staged by TMA gather4 (4 rows per instruction) through `vmap`, 32 rows x 32 floats per step
+                           // bit4: rows staged by TMA gather4 (4 rows per instruction) through `vmap`, 32 rows x 32 floats per step;
+                           // bit5: no whole-row L2 prefetch at the start of a hop
 };
 // grid = number of resident warps; returns cudaError
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);

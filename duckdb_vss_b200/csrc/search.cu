@@ -10,6 +10,8 @@ namespace gvss {
 __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
                                       const ScratchLayout &sl, int direct, const CUtensorMap *vmap) {
     w.g4 = (direct & 16) != 0;
+    w.prefetch_rows = (direct & 32) == 0;
+    w.prefetch_vis = (direct & 64) == 0;
     w.vmap = vmap;
     w.direct = (direct & 1) != 0;
     w.spec_prefetch = (direct & 2) != 0;
