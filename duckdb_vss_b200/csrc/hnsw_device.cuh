@@ -51,6 +51,27 @@ struct Cand {
     uint32_t s;
 };
 
+// Operation counts for kernel tuning (build with -DGVSS_OPCOUNT=1; read with the debug hook gvssdbg_opcounts). Off in the
+// shipped library: OPC() compiles to nothing.
+#ifndef GVSS_OPCOUNT
+#define GVSS_OPCOUNT 0
+#endif
+#ifndef GVSS_VSHIFT
+#define GVSS_VSHIFT 1 // result-list insertion moves 128-element blocks (4 per lane) instead of 32-element windows (+5 % QPS)
+#endif
+#if GVSS_OPCOUNT
+enum { kOpQueries, kOpHops, kOpNew, kOpHopsLe16, kOpHopsNone, kOpPushes, kOpPrunes, kOpPruneKept, kOpInsBatches, kOpInserted,
+       kOpShifted, kOpVisRounds, kOpMaybeBatches, kOpPushLevels, kOpPopLevels, kOpClkSelect, kOpClkGather, kOpClkDist, kOpClkMerge,
+       kOpClkStage, kOpClkWait, kOpClkMath, kOpSteps, kOpClkTotal, kOpClkAccept, kOpClkShift, kOpClkAdj, kOpClkVis, kOpClkShiftLoop, kOpCount };
+static __device__ unsigned long long g_opcount[kOpCount];
+// per-warp, flushed once per query by k_search; GVSS_OPCOUNT=2 keeps only the phase clocks (less distortion)
+#define OPC(i, v) do { if (GVSS_OPCOUNT == 1 || (i) >= kOpClkSelect || (i) == kOpQueries) w.opc[i] += (unsigned long long)(v); } while (0)
+#define OPCLK(var) const long long var = clock64()
+#else
+#define OPC(i, v) do { } while (0)
+#define OPCLK(var) do { } while (0)
+#endif
+
 // Per-warp workspace: shared-memory carve-out + global scratch (visited table, queue overflow).
 struct WarpWs {
     float *q;            // dpad floats: the query / the vector being inserted
@@ -79,6 +100,9 @@ struct WarpWs {
     uint32_t *bitmap;    // exact fallback: one bit per node, used when a search would overfill the table
     uint32_t bitmap_words;
     bool use_bitmap;
+#if GVSS_OPCOUNT
+    unsigned long long opc[kOpCount];
+#endif
     uint64_t *mbar;      // 2 mbarriers (one per stage buffer)
     uint32_t phase[2];
 };
@@ -88,19 +112,6 @@ struct Counters {
     uint32_t flags; // bit0: visited table / queue overflow; bit31: trace this query (debug aid, GVSS_TRACE_QUERY)
 };
 
-// Operation counts for kernel tuning (build with -DGVSS_OPCOUNT=1; read with the debug hook gvssdbg_opcounts). Off in the
-// shipped library: OPC() compiles to nothing.
-#ifndef GVSS_OPCOUNT
-#define GVSS_OPCOUNT 0
-#endif
-#if GVSS_OPCOUNT
-enum { kOpQueries, kOpHops, kOpNew, kOpHopsLe16, kOpHopsNone, kOpPushes, kOpPrunes, kOpPruneKept, kOpInsBatches, kOpInserted,
-       kOpShifted, kOpVisRounds, kOpMaybeBatches, kOpPushLevels, kOpPopLevels, kOpCount };
-static __device__ unsigned long long g_opcount[kOpCount];
-#define OPC(i, v) do { if (lane_id() == 0) atomicAdd(&g_opcount[i], (unsigned long long)(v)); } while (0)
-#else
-#define OPC(i, v) do { } while (0)
-#endif
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -255,9 +266,12 @@ __device__ __noinline__ float direct_distance(const float *vectors, uint32_t dpa
     return acc_finish<METRIC>(acc);
 }
 
-// Query-to-node distances with gather4 staging: lane i <-> row i for all 32 lanes, 32 floats (one 128-byte line) of every
-// row per step. Lane 4j issues the copy for lanes 4j..4j+3 (inactive lanes name a row outside the tensor: zero fill, no
-// traffic). Reads are conflict-free: in each 8-lane phase of an LDS.128 the swizzle spreads the lanes over all 8 granules.
+// Query-to-node distances with gather4 staging: lane i <-> row i. The 4 KB stage holds 32 rows x one 128-byte line, or —
+// when a batch has at most 16 / 8 rows — 16 rows x 2 lines / 8 rows x 4 lines, so that small batches need fewer
+// fetch-wait-compute steps. Sub-tile k (line ch0 + k of the rows) starts at stage + k * rows_cap * 128 B; lane L with
+// L % 4 == 0 issues the copy for sub-tile L / rows_cap, rows (L % rows_cap) .. +3 (inactive lanes name a row outside the
+// tensor: zero fill, no traffic), which lands at stage + L * 128 B. Reads are conflict-free: in each 8-lane phase of an
+// LDS.128 the TMA swizzle (granule ^ row % 8) spreads the lanes over all 8 granules of a line.
 constexpr int kG4Chunk = 32;
 constexpr int kG4OobRow = 0x7FFFFFFF;
 template <int METRIC>
@@ -265,43 +279,54 @@ __device__ __forceinline__ float warp_distances_g4(const GraphView &g, WarpWs &w
     const uint32_t lane = lane_id();
     const uint32_t amask = __ballot_sync(kFull, active);
     if (!amask) return 0.0f;
-    // groups of 4 lanes with at least one active lane
-    uint32_t gm = amask | (amask >> 1);
-    gm = (gm | (gm >> 2)) & 0x11111111u;
-    const uint32_t ngroups = __popc(gm);
-    const int r0 = active ? (int)my_slot : kG4OobRow;
-    const int r1 = __shfl_down_sync(kFull, r0, 1), r2 = __shfl_down_sync(kFull, r0, 2), r3 = __shfl_down_sync(kFull, r0, 3);
-    const bool issuer = (gm >> lane) & 1u;
-    float *sbuf = w.stage[0];
+    const uint32_t n = 32u - (uint32_t)__clz(amask);          // rows 0..n-1 (callers use a prefix of the lanes)
+    const uint32_t rows_cap = n <= 8u ? 8u : (n <= 16u ? 16u : 32u);
+    const uint32_t cpt = 32u / rows_cap;                        // 128-byte lines of a row per step
     const uint32_t nchunks = (g.dpad + kG4Chunk - 1) / kG4Chunk;
-    const float4 *myrow = reinterpret_cast<const float4 *>(sbuf + lane * kG4Chunk);
+    const int r0 = active ? (int)my_slot : kG4OobRow;
+    const uint32_t grow = lane & (rows_cap - 1u), gk = lane / rows_cap; // as issuer: first row of my group, my sub-tile
+    const int ra = __shfl_sync(kFull, r0, grow), rb = __shfl_sync(kFull, r0, grow + 1u), rc = __shfl_sync(kFull, r0, grow + 2u),
+              rd = __shfl_sync(kFull, r0, grow + 3u);
+    const bool issuer_row = (lane & 3u) == 0u && ((amask >> grow) & 0xFu) != 0u;
+    float *sbuf = w.stage[0];
     const uint32_t sw = lane & 7u;
     Acc acc = {0.0f, 0.0f, 0.0f};
-    for (uint32_t ch = 0; ch < nchunks; ch++) {
-        if (lane == 0) mbar_expect_tx(w.mbar, ngroups * 4u * kG4Chunk * 4u);
+    for (uint32_t ch0 = 0; ch0 < nchunks; ch0 += cpt) {
+        OPCLK(t0);
+        const bool issuer = issuer_row && ch0 + gk < nchunks;
+        const uint32_t nissue = __popc(__ballot_sync(kFull, issuer));
+        if (lane == 0) mbar_expect_tx(w.mbar, nissue * 4u * kG4Chunk * 4u);
         __syncwarp();
-        if (issuer) tma_gather4(sbuf + lane * kG4Chunk, w.vmap, (int)(ch * kG4Chunk), r0, r1, r2, r3, w.mbar);
+        if (issuer) tma_gather4(sbuf + lane * kG4Chunk, w.vmap, (int)((ch0 + gk) * kG4Chunk), ra, rb, rc, rd, w.mbar);
+        OPCLK(t1);
         mbar_wait(w.mbar, w.phase[0]);
+        OPCLK(t2);
         w.phase[0] ^= 1u;
         if (active) {
-            const uint32_t nfl = min((uint32_t)kG4Chunk, g.dpad - ch * kG4Chunk);
-            const float4 *a = reinterpret_cast<const float4 *>(w.q + ch * kG4Chunk);
-            if (nfl == kG4Chunk) {
+            for (uint32_t k = 0; k < cpt && ch0 + k < nchunks; k++) {
+                const uint32_t ch = ch0 + k;
+                const uint32_t nfl = min((uint32_t)kG4Chunk, g.dpad - ch * kG4Chunk);
+                const float4 *a = reinterpret_cast<const float4 *>(w.q + ch * kG4Chunk);
+                const float4 *myrow = reinterpret_cast<const float4 *>(sbuf + (k * rows_cap + lane) * kG4Chunk);
+                if (nfl == kG4Chunk) {
 #pragma unroll
-                for (uint32_t i = 0; i < kG4Chunk / 4; i++) {
-                    const float4 x = a[i], y = myrow[i ^ sw];
-                    acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
-                    acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
-                }
-            } else {
-                for (uint32_t i = 0; i < nfl / 4; i++) {
-                    const float4 x = a[i], y = myrow[i ^ sw];
-                    acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
-                    acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                    for (uint32_t i = 0; i < kG4Chunk / 4; i++) {
+                        const float4 x = a[i], y = myrow[i ^ sw];
+                        acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
+                        acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                    }
+                } else {
+                    for (uint32_t i = 0; i < nfl / 4; i++) {
+                        const float4 x = a[i], y = myrow[i ^ sw];
+                        acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
+                        acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                    }
                 }
             }
         }
         __syncwarp(); // all lanes are done reading the buffer before it is refilled
+        OPCLK(t3);
+        OPC(kOpClkStage, t1 - t0); OPC(kOpClkWait, t2 - t1); OPC(kOpClkMath, t3 - t2); OPC(kOpSteps, 1);
     }
     return active ? acc_finish<METRIC>(acc) : 0.0f;
 }
@@ -742,6 +767,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     __syncwarp();
 
     for (;;) {
+        OPCLK(t_sel);
         Cand c;
         uint32_t next_slot = kInvalid; // most likely next candidate (prefetch hint)
         if constexpr (LQ) {
@@ -792,12 +818,15 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         if ((cnt.flags & 0x80000000u) && lane == 0)
             printf("pop %u slot %u d %.9g radius %.9g heap %u top %u computed %u\n", cnt.base, c.s, c.d, radius, heap_size, top_size, cnt.computed);
         if (INSERT && c.s == new_slot) continue;
+        uint32_t pcap = 0;
+        const uint32_t *plist = nullptr;
         if (next_slot != kInvalid) { // pull its adjacency row towards L2
-            uint32_t pcap;
-            const uint32_t *plist = list_ptr(g, next_slot, level, pcap);
+            plist = list_ptr(g, next_slot, level, pcap);
             if (lane * 32 < pcap) prefetch_l2(plist + lane * 32);
         }
 
+        OPCLK(t_gather);
+        OPC(kOpClkSelect, t_gather - t_sel);
         // 1. unvisited neighbours, compacted in list order (visits.set(): the first occurrence wins)
         uint32_t cap;
         const uint32_t *list = list_ptr(g, c.s, level, cap);
@@ -811,6 +840,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const uint32_t idx = base + lane;
             const uint32_t s = idx < cap ? ld_adj<VOLATILE>(list + idx) : kInvalid;
             if (!__ballot_sync(kFull, s != kInvalid)) break;
+            OPCLK(t_v0);
+            if (base == 0) OPC(kOpClkAdj, t_v0 - t_gather);
             const bool valid = s != kInvalid && s < g.count;
             if (w.spec_prefetch && valid) { // start pulling the row towards L2 while the visited test is in flight
                 const float *row = g.vectors + (size_t)s * g.dpad;
@@ -821,6 +852,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const bool room = w.use_bitmap || nvis < w.vis_limit;
             const bool isnew = vis_insert_warp(w, s, leader && room);
             const uint32_t nmask = __ballot_sync(kFull, isnew);
+            OPCLK(t_v1);
+            OPC(kOpClkVis, t_v1 - t_v0);
             if (!room && __ballot_sync(kFull, leader)) cnt.flags |= 1u;
             if (isnew) w.nb[nnew + __popc(nmask & lt_mask)] = s;
             nnew += __popc(nmask);
@@ -833,13 +866,22 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         if (!nnew) continue;
         cnt.computed += nnew;
 
+        // the likely next candidate's list has reached L2 by now: read it, and after the distance phase start the visited
+        // windows of ITS neighbours on their way from DRAM (a hint only: wrong guesses cost 32 bytes of traffic each)
+        uint32_t sp0 = kInvalid, sp1 = kInvalid;
+        if (w.prefetch_vis && !w.use_bitmap && plist) {
+            if (lane < pcap) sp0 = ld_adj<VOLATILE>(plist + lane);
+            if (32 + lane < pcap) sp1 = ld_adj<VOLATILE>(plist + 32 + lane);
+        }
+        OPCLK(t_dist);
+        OPC(kOpClkGather, t_dist - t_gather);
         // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
         const uint32_t bw = ((GVSS_DIRECT_PATH && w.direct) || w.g4) ? 32u : w.stage_rows; // rows per distance batch
         if (w.g4 && w.prefetch_rows) {
             // gather4 staging takes one 128-byte line of every row per step: get ALL lines of all new rows moving towards L2
             // now, so that only the first step of the hop waits for DRAM
             const uint32_t lines = (g.dpad * 4 + 127) / 128;
-            for (uint32_t i = lane; i < nnew * lines; i += 32) {
+            for (uint32_t i = lane; i < nnew * lines; i += 32) { // consecutive lanes <-> consecutive lines of a row (measured best)
                 const uint32_t r = i / lines, l = i - r * lines;
                 if (r || l) prefetch_l2(g.vectors + (size_t)w.nb[r] * g.dpad + l * 32);
             }
@@ -859,6 +901,10 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         }
         __syncwarp();
 
+        if (sp0 != kInvalid) prefetch_l2(w.vis + (((sp0 * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1)));
+        if (sp1 != kInvalid) prefetch_l2(w.vis + (((sp1 * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1)));
+        OPCLK(t_merge);
+        OPC(kOpClkDist, t_merge - t_dist);
         // 3. acceptance, queue and result-list update, 32 candidates at a time
         for (uint32_t b = 0; b < nnew; b += 32) {
             const bool have = b + lane < nnew;
@@ -869,6 +915,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const bool maybe = have && (top_size < limit || dj < radius);
             if (!__ballot_sync(kFull, maybe)) continue;
             OPC(kOpMaybeBatches, 1);
+            OPCLK(t_a0);
             const bool allowed = maybe && (INSERT || !g.has_deleted || __ldg(&g.keys[sj]) != INT64_MAX);
             const uint32_t amask = __ballot_sync(kFull, allowed);
             // list size and order statistic as the reference would see them just before candidate j
@@ -882,6 +929,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             const uint32_t le_top = maybe ? top_upper_bound(w.top_d, top_size, dj) : 0u;
             const bool acc = maybe && (size_before < limit || le_top + le_prev < limit);
             const uint32_t accmask = __ballot_sync(kFull, acc);
+            OPCLK(t_a1);
+            OPC(kOpClkAccept, t_a1 - t_a0);
             if (!accmask) continue;
 
             OPC(kOpPushes, __popc(accmask));
@@ -917,6 +966,54 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                 OPC(kOpInsBatches, 1);
                 OPC(kOpInserted, m_ins);
                 OPC(kOpShifted, top_size - pmin);
+                // old elements [pmin, top_size) move up by the number of insertions at or before them. The insertion points go
+                // to shared memory in ascending order (this batch's slice of w.nd is dead: dj/sj live in registers), then
+                // aligned blocks of 128 elements are moved from the top down, 4 consecutive elements per lane: all reads of a
+                // block happen before its writes, and writes only reach upwards into blocks that were already moved.
+                OPCLK(t_s0);
+                OPC(kOpClkMerge, t_s0 - t_a1);
+#if GVSS_VSHIFT
+                uint32_t *ins_lb = reinterpret_cast<uint32_t *>(w.nd + b);
+                __syncwarp();
+                if (ins) ins_lb[before] = lb;
+                __syncwarp();
+                for (int32_t blk = pmin < top_size ? (int32_t)((top_size - 1u) >> 7) : -1; blk >= (int32_t)(pmin >> 7); blk--) {
+                    const uint32_t i0 = (uint32_t)blk * 128u + lane * 4u;
+                    const bool any = i0 < top_size && i0 + 3u >= pmin;
+                    float4 td = make_float4(0.f, 0.f, 0.f, 0.f);
+                    uint4 ts = make_uint4(0u, 0u, 0u, 0u);
+                    uint32_t sh0 = 0, sh1 = 0, sh2 = 0, sh3 = 0;
+                    if (any) {
+                        td = *reinterpret_cast<const float4 *>(w.top_d + i0);
+                        ts = *reinterpret_cast<const uint4 *>(w.top_s + i0);
+#pragma unroll 4
+                        for (uint32_t r = 0; r < m_ins; r++) {
+                            const uint32_t pa = ins_lb[r];
+                            sh0 += pa <= i0 ? 1u : 0u;
+                            sh1 += pa <= i0 + 1u ? 1u : 0u;
+                            sh2 += pa <= i0 + 2u ? 1u : 0u;
+                            sh3 += pa <= i0 + 3u ? 1u : 0u;
+                        }
+                    }
+                    __syncwarp();
+                    if (any) {
+                        const float tdv[4] = {td.x, td.y, td.z, td.w};
+                        const uint32_t tsv[4] = {ts.x, ts.y, ts.z, ts.w};
+                        const uint32_t shv[4] = {sh0, sh1, sh2, sh3};
+#pragma unroll
+                        for (uint32_t e = 0; e < 4; e++) {
+                            const uint32_t i = i0 + e;
+                            if (i >= pmin && i < top_size) {
+                                if (i + shv[e] < limit) { w.top_d[i + shv[e]] = tdv[e]; w.top_s[i + shv[e]] = tsv[e]; }
+                                else if constexpr (LQ) {
+                                    if (!(tsv[e] & kExpanded)) { dropped = fminf(dropped, tdv[e]); has_drop = true; }
+                                }
+                            }
+                        }
+                    }
+                    __syncwarp();
+                }
+#else
                 // old elements [pmin, top_size) move up by the number of insertions at or before them; windows from the top
                 for (int32_t hi = (int32_t)top_size; hi > (int32_t)pmin; hi -= 32) {
                     const int32_t i = hi - 1 - (int32_t)lane;
@@ -935,6 +1032,9 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     }
                     __syncwarp();
                 }
+#endif
+                OPCLK(t_s1);
+                OPC(kOpClkShiftLoop, t_s1 - t_s0);
                 if (ins && lb + before < limit) { w.top_d[lb + before] = dj; w.top_s[lb + before] = sj; }
                 top_size = min(limit, top_size + m_ins);
                 __syncwarp();
@@ -948,6 +1048,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                         ghost = fminf(ghost, __uint_as_float(u));
                     }
                 }
+                OPCLK(t_a2);
+                OPC(kOpClkShift, t_a2 - t_a1);
             }
         }
     }

@@ -72,6 +72,9 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         Counters cnt = {0, 0, 0, (long long)qi == p.trace_query ? 0x80000000u : 0u};
         uint32_t top_size = 0;
         OPC(kOpQueries, 1);
+#if GVSS_OPCOUNT
+        for (int i = 0; i < kOpCount; i++) w.opc[i] = i == kOpQueries ? 1ull : 0ull;
+#endif
         if (g.count && p.k) {
             const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
             const Counters before = cnt;
@@ -79,6 +82,7 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
             // the exact bitmap (flag bit1), one that meets an exact tie with usearch's heap as the queue (flag bit2)
             const bool lq_ok = !g.has_deleted && (p.direct & 8) == 0;
             bool lq = lq_ok, bitmap = false;
+            OPCLK(t_q0);
             for (;;) {
                 cnt = before;
                 w.use_bitmap = bitmap;
@@ -88,6 +92,8 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
                 if (lq && (cnt.flags & 4u)) { lq = false; continue; }
                 break;
             }
+            OPCLK(t_q1);
+            OPC(kOpClkTotal, t_q1 - t_q0);
             w.use_bitmap = false;
             cnt.flags = (cnt.flags & ~6u) | (bitmap ? 2u : 0u) | (!lq && lq_ok ? 4u : 0u);
         }
@@ -97,6 +103,9 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
             p.keys_out[qi * p.k + i] = have ? __ldg(&g.keys[w.top_s[i] & kSlotMask]) : -1; // dump_to: slot -> key, index.hpp:2252-2258
             if (p.dist_out) p.dist_out[qi * p.k + i] = have ? w.top_d[i] : CUDART_INF_F;
         }
+#if GVSS_OPCOUNT
+        if (lane == 0) for (int i = 0; i < kOpCount; i++) atomicAdd(&g_opcount[i], w.opc[i]);
+#endif
         if (lane == 0) {
             if (p.counts_out) p.counts_out[qi] = n;
             if (p.stats_out) p.stats_out[qi] = gvss_search_stats{cnt.computed, cnt.cycles, cnt.base, cnt.flags & 0x7FFFFFFFu};
