@@ -18,7 +18,7 @@ __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, cons
     w.g4 = false; // the build stages whole rows (neighbour selection re-reads them); gather4 staging is a search path
     w.vmap = nullptr;
     w.prefetch_rows = false;
-    w.prefetch_vis = false;
+    w.prefetch_vis = (direct & 64) == 0;
     w.direct = (direct & 1) != 0;
     w.spec_prefetch = (direct & 2) != 0;
     w.use_tma = (direct & 4) == 0;
@@ -207,13 +207,21 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         for (int l = min(level, max_level); l >= 0; --l) {
             uint32_t top_size = 0;
             t0 = clock64();
-            beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
-            if (cnt.flags & 1u) { // visited table would have overfilled: redo the level with the exact bitmap
+            // list-as-queue first; a level that would overfill the visited table is redone with the exact bitmap, one that
+            // meets an exact tie with usearch's heap as the queue (same scheme as k_search)
+            bool lq = (p.direct & 8) == 0, bitmap = false;
+            for (;;) {
                 cnt.flags = 0;
-                w.use_bitmap = true;
-                beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
-                w.use_bitmap = false;
+                w.use_bitmap = bitmap;
+                if (lq) beam_search<METRIC, true, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
+                else beam_search<METRIC, true, true, false>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
+                if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
+                if (lq && (cnt.flags & 4u)) { lq = false; continue; }
+                break;
             }
+            w.use_bitmap = false;
+            if (lq) for (uint32_t i = lane; i < top_size; i += 32) w.top_s[i] &= kSlotMask; // drop the expanded flags
+            __syncwarp();
 
             // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)
             const uint32_t cap_l = l ? g.M : g.M0;
