@@ -207,20 +207,19 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         for (int l = min(level, max_level); l >= 0; --l) {
             uint32_t top_size = 0;
             t0 = clock64();
-            // list-as-queue first; a level that would overfill the visited table is redone with the exact bitmap, one that
-            // meets an exact tie with usearch's heap as the queue (same scheme as k_search)
+            // list-as-queue first; a level that would overfill the visited table is redone with the exact bitmap; exact ties
+            // switch to usearch's heap mid-flight (same scheme as k_search)
             bool lq = (p.direct & 8) == 0, bitmap = false;
             for (;;) {
                 cnt.flags = 0;
                 w.use_bitmap = bitmap;
-                if (lq) beam_search<METRIC, true, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
-                else beam_search<METRIC, true, true, false>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged);
+                beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged, lq);
                 if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
-                if (lq && (cnt.flags & 4u)) { lq = false; continue; }
+                if (cnt.flags & 8u) { lq = false; continue; }
                 break;
             }
             w.use_bitmap = false;
-            if (lq) for (uint32_t i = lane; i < top_size; i += 32) w.top_s[i] &= kSlotMask; // drop the expanded flags
+            for (uint32_t i = lane; i < top_size; i += 32) w.top_s[i] &= kSlotMask; // drop the expanded flags
             __syncwarp();
 
             // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)

@@ -729,25 +729,54 @@ __device__ __forceinline__ uint32_t top_upper_bound(const float *td, uint32_t n,
 //     existing ones going BEFORE them and later candidates before earlier equal ones (sorted_buffer_gt::insert uses
 //     lower_bound), cut at `limit`.
 //
-// LQ = true ("list as queue"): every candidate the reference can still pop is an unexpanded member of the result list
-// (an entry that fell off the list lies above the radius for good), and as long as no two such candidates have EQUAL
-// distances the heap pops them in ascending distance — i.e. in list order. The queue is then not materialised at all:
-// expanded members carry a flag in the top bit of their slot and the next candidate is the first unflagged entry. A
-// candidate that ties with a list member or with another candidate of its batch sets flag bit2 and ends the search; the
-// caller repeats it with the real heap (LQ = false), which keeps usearch's pop order among ties. Not used when the index
-// holds removed members (they enter the queue but not the list).
+// lq = true ("list as queue"): every candidate the reference can still pop is an unexpanded member of the result list
+// (an entry that fell off the list lies above the radius for good), and as long as the smallest live distance is unique
+// the heap pops candidates in ascending distance — i.e. in list order. The queue is then not materialised: expanded
+// members carry a flag in the top bit of their slot and the next candidate is the first unflagged entry; the queue
+// operations the reference would have done (pushes of accepted candidates, one pop per expansion) are only LOGGED, 8
+// bytes each, at the far end of the queue's overflow area. When two live candidates tie for the head of the queue — or
+// an entry that fell off the list equals it — the pop order depends on the history of usearch's heap: the log is
+// replayed on the real heap (cheap: no distance is recomputed) and the search continues with the heap as the queue
+// (flag bit2). If the log ran out of room the search ends with flag bit3 and the caller repeats it with lq = false.
+// Not used when the index holds removed members (they enter the queue but not the list).
 constexpr uint32_t kExpanded = 0x80000000u;
 constexpr uint32_t kSlotMask = 0x7FFFFFFFu;
 
-template <int METRIC, bool INSERT, bool VOLATILE, bool LQ = false>
+template <int METRIC, bool INSERT, bool VOLATILE>
 __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, uint32_t limit, int level,
-                                            uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged) {
+                                            uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged, bool lq = false) {
     const uint32_t lane = lane_id();
     const uint32_t lt_mask = (1u << lane) - 1u;
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
     uint32_t scan_from = 0; // LQ: every list entry before this index is expanded
     float ghost = CUDART_INF_F; // LQ: smallest distance among the live entries that fell off the list (still in the reference's queue)
+    // LQ: log of the reference's queue operations, written downwards from the end of the overflow area ({d, slot} = push,
+    // slot == kInvalid = pop); it may use half of the area, the replayed heap then fits below it
+    const uint32_t log_end = w.heap_total - w.heap_smem, log_cap = log_end / 2;
+    uint32_t logn = 0;
+    bool log_ok = true;
+    auto log_put = [&](uint32_t at, float d, uint32_t s) { w.heap_ovf[log_end - 1u - at] = Cand{d, s}; };
+    // replays the log on usearch's heap and leaves list-as-queue mode; false (flag bit3) when the log is incomplete
+    auto to_heap = [&]() -> bool {
+        if (!log_ok) { cnt.flags |= 8u; return false; }
+        __syncwarp();
+        heap_size = 0;
+        for (uint32_t base = 0; base < logn; base += 32) {
+            Cand mine = {0.0f, kInvalid};
+            if (base + lane < logn) mine = w.heap_ovf[log_end - 1u - (base + lane)];
+            const uint32_t nb = min(32u, logn - base);
+            for (uint32_t j = 0; j < nb; j++) {
+                const float d = __shfl_sync(kFull, mine.d, j);
+                const uint32_t s = __shfl_sync(kFull, mine.s, j);
+                if (s == kInvalid) heap_pop(w, heap_size);
+                else heap_push(w, heap_size, d, s);
+            }
+        }
+        lq = false;
+        cnt.flags |= 4u;
+        return true;
+    };
     top_size = 0;
     vis_clear(w);
 
@@ -755,7 +784,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     radius = __shfl_sync(kFull, radius, 0);
     if (radius != radius) radius = CUDART_INF_F;
     cnt.computed++;
-    if constexpr (!LQ) heap_push(w, heap_size, radius, start);
+    if (!lq) heap_push(w, heap_size, radius, start);
+    else { if (lane == 0) log_put(0, radius, start); logn = 1; }
     if (lane == 0) vis_insert(w, start);
     const bool start_ok = INSERT || !g.has_deleted || __ldg(&g.keys[start]) != INT64_MAX;
     if (start_ok) {
@@ -770,7 +800,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         OPCLK(t_sel);
         Cand c;
         uint32_t next_slot = kInvalid; // most likely next candidate (prefetch hint)
-        if constexpr (LQ) {
+        if (lq) {
             uint32_t cur = top_size, nxt = top_size;
             bool later = false; // the next unexpanded entry (if any) lies beyond the window that holds `cur`
             for (uint32_t i0 = scan_from & ~31u; i0 < top_size; i0 += 32) {
@@ -785,23 +815,31 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     break;
                 }
             }
+            bool tie;
             if (cur >= top_size) {
                 // nothing left to expand: the reference's queue is empty or its head fell off the list earlier, i.e. lies
                 // above the radius and ends the search — unless it EQUALS the radius, then the reference expands it
-                if (top_size == limit && ghost == radius) cnt.flags |= 4u;
-                break;
+                tie = top_size == limit && ghost == radius;
+                if (!tie) break;
+            } else {
+                c.d = w.top_d[cur];
+                c.s = w.top_s[cur] & kSlotMask;
+                // an entry outside the list, or a second live candidate, at the same distance as the queue head: the
+                // reference's pop order depends on its heap's history (`later`: conservative, the equal entry may be expanded)
+                tie = c.d == ghost || (nxt < top_size && w.top_d[nxt] == c.d);
+                if (!tie && nxt < top_size && !later) next_slot = w.top_s[nxt] & kSlotMask;
             }
-            c.d = w.top_d[cur];
-            c.s = w.top_s[cur] & kSlotMask;
-            if (c.d == ghost) { cnt.flags |= 4u; return; } // an entry outside the list ties with the queue head
-            if (nxt < top_size) {
-                // two live candidates at the same distance: the reference's pop order depends on its heap's history
-                // (`later`: conservative, the equal entry may already be expanded)
-                if (w.top_d[nxt] == c.d) { cnt.flags |= 4u; return; }
-                if (!later) next_slot = w.top_s[nxt] & kSlotMask;
+            if (tie) {
+                if (!to_heap()) return;
+                continue; // the same iteration again, with the heap as the queue
             }
             __syncwarp();
-            if (lane == 0) w.top_s[cur] = c.s | kExpanded;
+            if (lane == 0) {
+                w.top_s[cur] = c.s | kExpanded;
+                if (logn < log_cap) log_put(logn, 0.0f, kInvalid);
+            }
+            log_ok = log_ok && logn < log_cap;
+            logn++;
             __syncwarp();
             scan_from = cur + 1;
         } else {
@@ -934,12 +972,18 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             if (!accmask) continue;
 
             OPC(kOpPushes, __popc(accmask));
-            if constexpr (!LQ) {
+            if (!lq) {
                 for (uint32_t m = accmask; m; m &= m - 1) { // next.insert in list order
                     const uint32_t i = __ffs(m) - 1;
-                    if (w.heap_smem && heap_size == w.heap_smem && top_size == limit) heap_prune(w, heap_size, radius);
+                    // (pruning rebuilds the heap, so it is only allowed where the queue was never list-shaped: heap_smem >= 256)
+                    if (w.heap_smem >= 256u && heap_size == w.heap_smem && top_size == limit) heap_prune(w, heap_size, radius);
                     if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
                 }
+            } else { // log the pushes in list order
+                const uint32_t at = logn + __popc(accmask & lt_mask);
+                if (acc && at < log_cap) log_put(at, dj, sj);
+                logn += __popc(accmask);
+                log_ok = log_ok && logn <= log_cap;
             }
 
             const bool ins = acc && allowed;
@@ -957,7 +1001,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                 // reference's queue; harmless there unless the queue head ever EQUALS one of them)
                 float dropped = CUDART_INF_F;
                 bool has_drop = false;
-                if constexpr (LQ) {
+                if (lq) {
                     const uint32_t at = (ins && lb + before < limit) ? lb + before : 0xFFFFFFFFu;
                     scan_from = min(scan_from, __reduce_min_sync(kFull, at));
                     if (ins && lb + before >= limit) { dropped = dj; has_drop = true; }
@@ -1005,7 +1049,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                             const uint32_t i = i0 + e;
                             if (i >= pmin && i < top_size) {
                                 if (i + shv[e] < limit) { w.top_d[i + shv[e]] = tdv[e]; w.top_s[i + shv[e]] = tsv[e]; }
-                                else if constexpr (LQ) {
+                                else if (lq) {
                                     if (!(tsv[e] & kExpanded)) { dropped = fminf(dropped, tdv[e]); has_drop = true; }
                                 }
                             }
@@ -1027,7 +1071,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     }
                     __syncwarp();
                     if (mv && (uint32_t)i + sh < limit) { w.top_d[i + sh] = td; w.top_s[i + sh] = ts; }
-                    if constexpr (LQ) {
+                    if (lq) {
                         if (mv && (uint32_t)i + sh >= limit && !(ts & kExpanded)) { dropped = fminf(dropped, td); has_drop = true; }
                     }
                     __syncwarp();
@@ -1039,7 +1083,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                 top_size = min(limit, top_size + m_ins);
                 __syncwarp();
                 radius = w.top_d[top_size - 1];
-                if constexpr (LQ) {
+                if (lq) {
                     if (__ballot_sync(kFull, has_drop)) {
                         uint32_t u = __float_as_uint(dropped); // order-preserving key for the warp-wide minimum
                         u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);

@@ -78,24 +78,24 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         if (g.count && p.k) {
             const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
             const Counters before = cnt;
-            // fast path first (list as queue, hashed visited table); a query that would overfill the table is redone with
-            // the exact bitmap (flag bit1), one that meets an exact tie with usearch's heap as the queue (flag bit2)
+            // list-as-queue first (hashed visited table); a query that would overfill the table is redone with the exact
+            // bitmap (flag bit1); exact ties switch to usearch's heap mid-flight (flag bit2), or — if the operation log ran
+            // out of room — repeat the query with the heap from the start
             const bool lq_ok = !g.has_deleted && (p.direct & 8) == 0;
             bool lq = lq_ok, bitmap = false;
             OPCLK(t_q0);
             for (;;) {
                 cnt = before;
                 w.use_bitmap = bitmap;
-                if (lq) beam_search<METRIC, false, false, true>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
-                else beam_search<METRIC, false, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged);
+                beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged, lq);
                 if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
-                if (lq && (cnt.flags & 4u)) { lq = false; continue; }
+                if (cnt.flags & 8u) { lq = false; continue; }
                 break;
             }
             OPCLK(t_q1);
             OPC(kOpClkTotal, t_q1 - t_q0);
             w.use_bitmap = false;
-            cnt.flags = (cnt.flags & ~6u) | (bitmap ? 2u : 0u) | (!lq && lq_ok ? 4u : 0u);
+            cnt.flags = (cnt.flags & ~0xAu) | (bitmap ? 2u : 0u) | (!lq && lq_ok ? 4u : 0u);
         }
         const uint32_t n = min(top_size, p.k); // top.shrink(wanted), index.hpp:2526-2527
         for (uint32_t i = lane; i < p.k; i += 32) {
