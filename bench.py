@@ -358,7 +358,7 @@ def main():
         achieved = algo_bytes / t_kernel / 1e9
         traffic = None  # dram read+write bytes of one launch from the committed ncu --set full capture of this exact config
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r1_search_traffic.json")))
+            tj = json.load(open(os.path.join(ROOT, "profiles", "r2_search_traffic.json")))
             c = tj["config"]
             if (c["n"], c["nq"], c["ef_search"], c["M"], c["dims"]) == (n, nq, ef, M, d):
                 traffic = tj["traffic_bytes_per_launch"]

@@ -68,6 +68,8 @@ typedef struct gvss_search_stats {
     uint32_t visited_members;    /* context_t::iteration_cycles delta = level-0 expansions + upper-level hops */
     uint32_t base_expansions;    /* level-0 expansions only */
     uint32_t flags;              /* bit1: hashed visited table overfilled, level 0 redone with the exact bitmap (results exact);
+                                    bit2: two candidates tied exactly for the head of the queue, the rest of the query ran with
+                                          usearch's binary heap as the queue to keep its pop order (results exact);
                                     bit0: candidate queue overflow (results of this query are not reliable) */
 } gvss_search_stats;
 
