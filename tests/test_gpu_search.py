@@ -71,6 +71,35 @@ def test_reference_built_graph_search_parity(metric, d, n, M, checker):
         np.testing.assert_array_equal(st["visited"], want["visited"].astype(np.uint32))
 
 
+@pytest.mark.parametrize("metric,d,n,levels", [("l2sq", 32, 12000, 4), ("ip", 24, 8000, 3), ("cosine", 16, 6000, 3)])
+def test_tie_heavy_integer_data_matches_reference_pop_order(metric, d, n, levels, checker):
+    """SIFT-like integer-valued vectors: distances are small integers, so live candidates tie for the head of the queue
+    all the time. The list-as-queue fast path must notice every such tie and continue with usearch's heap (flag bit2);
+    ids, order among ties, distance bits and traversal counters still equal the reference's on its own graph."""
+    Checker, kind = checker
+    rng = np.random.default_rng(7 + d)
+    base = rng.integers(0, levels, size=(n, d)).astype(np.float32)
+    q = rng.integers(0, levels, size=(200, d)).astype(np.float32)
+    base[:, 0] += 1.0  # no all-zero rows (cosine)
+    q[:, 0] += 1.0
+    ref = Checker(d, metric, M=8)
+    ref.reserve(n, 4)
+    ref.add_bulk(base, threads=4)
+    ix = gv.Index(d, metric, M=8)
+    ix.load(ref.save())
+    tied = 0
+    for ef in (10, 64, 200):
+        want = ref.search_batch(q, 10, ef)
+        keys, dist, counts, st = ix.ef_search(q, 10, ef, stats=True)
+        np.testing.assert_array_equal(keys, want["keys"], err_msg=f"{metric} ef={ef} ({kind})")
+        np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32))
+        np.testing.assert_array_equal(st["computed"], want["computed"].astype(np.uint32))
+        np.testing.assert_array_equal(st["visited"], want["visited"].astype(np.uint32))
+        assert (st["flags"] & 3 == 0).all()
+        tied += int((st["flags"] & 4 != 0).sum())
+    assert tied > 300  # the tie path really ran (3 x 200 queries)
+
+
 def test_removed_members_are_traversed_but_never_returned(checker):
     Checker, _ = checker
     n, d = 3000, 16
