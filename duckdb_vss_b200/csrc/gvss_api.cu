@@ -255,8 +255,8 @@ static int search_device_locked(gvss_index *x, const float *d_queries, uint64_t 
     p.entry = x->entry; p.max_level = x->max_level < 0 ? 0 : x->max_level;
     p.trace_query = -1;
     if (const char *e = getenv("GVSS_TRACE_QUERY")) p.trace_query = atoll(e);
-    p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
+    p.sl = make_scratch_layout(limit, x->count, list_cap);
     p.direct = search_mode_bits();
     const bool g4 = setup_gather4(x, p);
     p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false, g4);
@@ -480,8 +480,8 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     p.keys_out = keys_out; p.dist_out = dist_out; p.counts_out = counts_out; p.stats_out = stats_out;
     p.entry = x->entry; p.max_level = x->max_level < 0 ? 0 : x->max_level;
     p.trace_query = -1;
-    p.sl = make_scratch_layout(limit, x->count);
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
+    p.sl = make_scratch_layout(limit, x->count, list_cap);
     p.direct = search_mode_bits();
     const bool g4 = setup_gather4(x, p);
     p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false, g4);
@@ -911,7 +911,7 @@ static int flush_locked(gvss_index *x) {
     p.ef_add = x->cfg.expansion_add;
     const uint32_t cmax = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
-    p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh);
+    p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh, cmax);
     static const uint32_t build_rows = [] { const char *e = getenv("GVSS_BUILD_STAGE_ROWS"); const uint32_t v = e ? (uint32_t)atoi(e) : 32u; return v == 16u ? 16u : 32u; }();
     p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, build_rows, true, cmax);
     p.direct = search_mode_bits();

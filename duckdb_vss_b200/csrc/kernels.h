@@ -28,7 +28,7 @@ struct ScratchLayout {
     uint32_t vis_slots, vis_limit, heap_ovf, bitmap_words;
     size_t bytes_per_warp;
 };
-ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes);
+ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes, uint32_t list_cap);
 
 struct SearchParams {
     const float *queries;

@@ -157,12 +157,16 @@ uint32_t default_heap_smem(uint32_t beam) {
     return (h + 31) / 32 * 32;
 }
 
-ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes) {
-    // visited members per search ~ 20*beam + 500 on the measured data sets; 64*beam slots
-    // (min 4096) keep the table under ~40 % load, the kernel flags a query that would exceed 75 %.
+ScratchLayout make_scratch_layout(uint32_t beam, uint64_t nodes, uint32_t list_cap) {
+    // A search expands about `beam` nodes and meets ~0.6 new members per listed neighbour on the measured data sets
+    // (1M x 128 at M0=64: 14.2k visited at beam 384; 1M x 768: 2.6k at beam 64), so beam * list_cap + 2048 slots keep the
+    // table around 45 % load; the kernel flags a query that would exceed 75 % and redoes it with the exact bitmap.
     ScratchLayout s{};
-    static const uint32_t factor = [] { const char *e = getenv("GVSS_VIS_FACTOR"); const uint32_t v = e ? (uint32_t)atoi(e) : 64u; return v ? v : 64u; }();
-    uint32_t want = beam * factor;
+    static const uint32_t factor = [] { const char *e = getenv("GVSS_VIS_FACTOR"); return e ? (uint32_t)atoi(e) : 0u; }();
+    const uint32_t per_beam = factor ? factor : (list_cap < 16u ? 16u : list_cap);
+    uint64_t want64 = (uint64_t)beam * per_beam + 2048u;
+    if (want64 > (1ull << 30)) want64 = 1ull << 30;
+    uint32_t want = (uint32_t)want64;
     if (want < 4096u) want = 4096u;
     uint32_t v = 4096u;
     while (v < want) v <<= 1;

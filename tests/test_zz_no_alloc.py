@@ -49,7 +49,7 @@ def test_noalloc_rejects_what_does_not_fit_and_staged_rows():
     ix.load(blob)
     q = torch.from_numpy(z["queries"]).cuda()
     out = torch.empty((q.shape[0], 16000), dtype=torch.int64, device="cuda")
-    with pytest.raises(gv.GvssError, match="scratch"):           # beam 16000 -> 1 Mi table slots x 12 B = 12 MiB per query slot > 1 MiB
+    with pytest.raises(gv.GvssError, match="scratch"):           # beam 16000 -> 512 Ki table slots x 12 B = 6 MiB per query slot > 1 MiB
         ix.search_device_noalloc(q.data_ptr(), q.shape[0], 16000, 16000, out.data_ptr())
     iy = gv.Index(3, "l2sq")
     iy.reserve(8, 1)
