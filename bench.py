@@ -236,6 +236,10 @@ def main():
     torch.cuda.synchronize()
     t_build = time.perf_counter() - t0
     build_launches = gv.lib().gvss_kernel_launches() - l0
+    bst = ix.build_stats()
+    # B_v = C_v*4d*w + H_v*(4+4*M0) + E_v*(4+4*M0), w = 1 for query-to-node, 2 for node-to-node distances
+    build_bytes = (bst["query_distances"] * 4.0 * d + bst["pair_distances"] * 8.0 * d + bst["base_expansions"] * (4 + 4.0 * M0)
+                   + bst["upper_expansions"] * (4 + 4.0 * M) + bst["rows_written"] * (4 + 4.0 * M0))
 
     # ---- ground truth (exact kernel, parity-checked against DuckDB's folds) and ef selection -------------------
     truth = torch.empty((nq, k), dtype=torch.int64, device=dev)
@@ -389,7 +393,14 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
             "build": {"value": build_vps, "unit": "vectors/s", "seconds": t_build, "kernel_launches": int(build_launches),
-                      "note": "gvss_add_batch_device + gvss_flush, rows resident in HBM, timed once before the steps"},
+                      "note": "gvss_add_batch_device + gvss_flush, rows resident in HBM, timed once before the steps (rank 0's counters below)",
+                      "per_vector": {"query_distances": bst["query_distances"] / max(1, bst["inserts"]),
+                                     "pair_distances": bst["pair_distances"] / max(1, bst["inserts"]),
+                                     "expansions": (bst["base_expansions"] + bst["upper_expansions"]) / max(1, bst["inserts"]),
+                                     "rows_written": bst["rows_written"] / max(1, bst["inserts"])},
+                      "roofline": {"bound": "hbm", "achieved": build_bytes / t_build / 1e9, "peak": peak, "unit": "GB/s",
+                                   "frac": build_bytes / t_build / 1e9 / peak, "kernel": "k_build<l2sq>",
+                                   "algorithmic_bytes": build_bytes, "note": "wall clock of the whole bulk build incl. uploads and the 16 ramp launches"}},
             "exact_topk": {"seconds": t_exact, "queries": nq, "base": n, "queries_per_s": nq / t_exact,
                            "note": "ground truth: tcgen05 3xTF32 candidate tiles + exact re-rank (bit-exact vs DuckDB folds), 2nd call, wall clock incl. plane split"},
             "wall_s_timed_region": t_wall,

@@ -28,6 +28,11 @@ class Info(C.Structure):
                 ("expansion_search", C.c_uint32), ("metric", C.c_char)]
 
 
+class BuildStats(C.Structure):
+    _fields_ = [("inserts", C.c_uint64), ("query_distances", C.c_uint64), ("pair_distances", C.c_uint64),
+                ("base_expansions", C.c_uint64), ("upper_expansions", C.c_uint64), ("rows_written", C.c_uint64)]
+
+
 class SearchStats(C.Structure):
     _fields_ = [("computed_distances", C.c_uint32), ("visited_members", C.c_uint32),
                 ("base_expansions", C.c_uint32), ("flags", C.c_uint32)]
@@ -59,6 +64,7 @@ SIGNATURES = {
     "gvss_serialized_length": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "gvss_get_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
     "gvss_get_level_stats": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(LevelStats)]),
+    "gvss_get_build_stats": (C.c_int, [C.c_void_p, C.POINTER(BuildStats)]),
     "gvss_exact_topk": (C.c_int, [C.c_char, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32,
                                   C.c_uint32, C.c_void_p, C.c_void_p]),
     "gvss_exact_topk_device": (C.c_int, [C.c_char, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64,

@@ -88,7 +88,9 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
         const float cd = alive ? w.top_d[my] : 0.0f;
         const uint32_t nprev = nkept;
         for (uint32_t k = 0; k < nprev; k++) {
-            if (!__ballot_sync(kFull, alive)) break;
+            const uint32_t am0 = __ballot_sync(kFull, alive);
+            if (!am0) break;
+            w.n_pair += __popc(am0);
             const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, kept_s[k]}, cs, alive, staged);
             if (alive && d < cd) alive = false;
         }
@@ -102,7 +104,9 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
             nkept++;
             if (nkept == needed) break;
             const bool act = alive && lane > j;
-            if (__ballot_sync(kFull, act)) {
+            const uint32_t am1 = __ballot_sync(kFull, act);
+            w.n_pair += __popc(am1);
+            if (am1) {
                 // the kept candidate's own row usually sits in the stage already (row j, single-chunk rows): then the
                 // step needs no memory access at all
                 const bool resident = g.dpad <= (uint32_t)kChunk && w.stage_rows == 32 && __shfl_sync(kFull, staged, j) == sj;
@@ -121,7 +125,8 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
 // (reconnect_neighbor_nodes_, index.hpp:3279-3311). `d_tn` = d(target, nbr).
 template <int METRIC>
 __device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t *locks, uint32_t target, uint32_t nbr, float d_tn,
-                                         int level, uint32_t *kept_s, float *kept_d, uint32_t top_limit_all, uint32_t &staged) {
+                                         int level, uint32_t *kept_s, float *kept_d, uint32_t top_limit_all, uint32_t &staged,
+                                         bool count_d_tn = false) {
     const uint32_t lane = lane_id();
     uint32_t capc;
     uint32_t *clist = list_ptr(g, target, level, capc);
@@ -136,16 +141,19 @@ __device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t
     if (present) { unlock_node(locks, target); return; }
     if (cntc < capc) {
         if (lane == 0) clist[cntc] = nbr;
+        w.n_rows_written++;
         unlock_node(locks, target);
         return;
     }
     uint32_t tsz = 0;
+    if (count_d_tn) w.n_qdist++; // the reference measures d(target, new node) only here, when the list has to be re-pruned
     top_insert(w, tsz, top_limit_all, d_tn, nbr);
     for (uint32_t base = 0; base < capc; base += 32) {
         const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
         const bool act = e != kInvalid;
         const uint32_t am = __ballot_sync(kFull, act);
         if (!am) break;
+        w.n_pair += __popc(am);
         const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, target}, e, act, staged);
         for (uint32_t m = am; m; m &= m - 1) {
             const uint32_t j = __ffs(m) - 1;
@@ -154,6 +162,7 @@ __device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t
     }
     const uint32_t nk2 = refine<METRIC>(g, w, tsz, capc, kept_s, kept_d, staged);
     for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
+    w.n_rows_written++;
     unlock_node(locks, target);
 }
 
@@ -200,6 +209,10 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         const uint32_t entry = (uint32_t)(es & 0xFFFFFFFFull);
 
         Counters cnt = {0, 0, 0, 0};
+        w.n_pair = 0;
+        w.n_qdist = 0;
+        w.n_rows_written = 0;
+        uint32_t n_qdist = 0, n_base = 0;
         long long t0 = clock64(), t_beam = 0, t_refine = 0, t_conn = 0, t_recon = 0;
         uint32_t closest = greedy_descent<METRIC, true>(g, w, entry, max_level, level, cnt, staged);
         const long long t_greedy = clock64() - t0;
@@ -210,6 +223,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             // list-as-queue first; a level that would overfill the visited table is redone with the exact bitmap; exact ties
             // switch to usearch's heap mid-flight (same scheme as k_search)
             bool lq = (p.direct & 8) == 0, bitmap = false;
+            const uint32_t base_before = cnt.base;
             for (;;) {
                 cnt.flags = 0;
                 w.use_bitmap = bitmap;
@@ -219,6 +233,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                 break;
             }
             w.use_bitmap = false;
+            if (l == 0) n_base += cnt.base - base_before;
             for (uint32_t i = lane; i < top_size; i += 32) w.top_s[i] &= kSlotMask; // drop the expanded flags
             __syncwarp();
 
@@ -247,6 +262,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                 if (keep_extra && epos < capx) mylist[epos] = extra;
             }
             unlock_node(p.locks, slot);
+            w.n_rows_written++;
             closest = mine_s[0];
             t_conn += clock64() - t0; t0 = clock64();
 
@@ -257,7 +273,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                 if (close == slot) continue;
                 float dn = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
                 dn = __shfl_sync(kFull, dn, 0);
-                add_link<METRIC>(g, w, p.locks, close, slot, dn, l, kept_s, kept_d, top_limit_all, staged);
+                add_link<METRIC>(g, w, p.locks, close, slot, dn, l, kept_s, kept_d, top_limit_all, staged, true);
             }
             // Inserts that are in flight at the same time cannot find each other through the graph. Before this node
             // leaves, it measures its distance to every vector other warps are inserting right now and links both ways with
@@ -268,7 +284,9 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                     const uint32_t wi = base + lane;
                     const uint32_t x = wi < gridDim.x ? __ldcg(p.inflight + wi) : kInvalid;
                     const bool act = x != kInvalid && x != slot && x < g.count;
-                    if (!__ballot_sync(kFull, act)) continue;
+                    const uint32_t pm = __ballot_sync(kFull, act);
+                    if (!pm) continue;
+                    n_qdist += __popc(pm);
                     const float d = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, x, act, staged);
                     uint32_t cm = __ballot_sync(kFull, act && d < a_worst);
                     while (cm) {
@@ -281,7 +299,9 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                         bool dominated = false;
                         for (uint32_t b2 = 0; b2 < nk; b2 += 32) {
                             const bool a2 = b2 + lane < nk && mine_d[b2 + lane] <= dx;
-                            if (!__ballot_sync(kFull, a2)) continue;
+                            const uint32_t dm = __ballot_sync(kFull, a2);
+                            if (!dm) continue;
+                            w.n_pair += __popc(dm);
                             const float dxs = warp_distances<METRIC>(g, w, LeftSrc{nullptr, xs}, a2 ? mine_s[b2 + lane] : kInvalid, a2, staged);
                             dominated |= __ballot_sync(kFull, a2 && dxs < dx) != 0u;
                         }
@@ -294,6 +314,14 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             t_recon += clock64() - t0;
         }
         if (p.inflight && lane == 0) __stcg(p.inflight + blockIdx.x, kInvalid);
+        if (p.stats && lane == 0) {
+            atomicAdd(p.stats + 0, 1ull);
+            atomicAdd(p.stats + 1, (unsigned long long)(cnt.computed + n_qdist + w.n_qdist));
+            atomicAdd(p.stats + 2, (unsigned long long)w.n_pair);
+            atomicAdd(p.stats + 3, (unsigned long long)n_base);
+            atomicAdd(p.stats + 4, (unsigned long long)(cnt.cycles - n_base));
+            atomicAdd(p.stats + 5, (unsigned long long)w.n_rows_written);
+        }
         if (p.prof && lane == 0) {
             atomicAdd(p.prof + 0, (unsigned long long)t_greedy); atomicAdd(p.prof + 1, (unsigned long long)t_beam);
             atomicAdd(p.prof + 2, (unsigned long long)t_refine); atomicAdd(p.prof + 3, (unsigned long long)t_conn);

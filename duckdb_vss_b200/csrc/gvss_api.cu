@@ -68,6 +68,7 @@ struct gvss_index {
     int16_t *d_levels = nullptr;
     uint32_t *d_nbr0 = nullptr, *d_upper = nullptr, *d_upper_off = nullptr, *d_locks = nullptr;
     unsigned long long *d_entry_state = nullptr, *d_work = nullptr;
+    unsigned long long *d_build_stats = nullptr; // 6 counters summed by k_build (gvss_build_stats order)
     uint64_t capacity = 0, count = 0;           // count = graph nodes (incl. removed slots)
     uint64_t upper_cap = 0, upper_used = 0;      // in blocks of strideU u32
     uint8_t *d_scratch = nullptr;
@@ -313,7 +314,8 @@ int gvss_create(const gvss_config *config, gvss_index **out) {
     x->stride0 = (x->cfg.connectivity_base + 7) / 8 * 8;
     x->strideU = (x->cfg.connectivity + 7) / 8 * 8;
     if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc(&x->d_entry_state, 8) != cudaSuccess || cudaMalloc(&x->d_work, 8) != cudaSuccess) {
+        cudaMalloc(&x->d_entry_state, 8) != cudaSuccess || cudaMalloc(&x->d_work, 8) != cudaSuccess ||
+        cudaMalloc(&x->d_build_stats, 48) != cudaSuccess || cudaMemset(x->d_build_stats, 0, 48) != cudaSuccess) {
         delete x;
         return fail("gvss_create: CUDA initialisation failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
@@ -326,7 +328,7 @@ void gvss_destroy(gvss_index *x) {
     if (!x) return;
     cudaSetDevice(x->device);
     free_device(x);
-    cudaFree(x->d_entry_state); cudaFree(x->d_work);
+    cudaFree(x->d_entry_state); cudaFree(x->d_work); cudaFree(x->d_build_stats);
     cudaFree(x->d_q); cudaFree(x->d_ok); cudaFree(x->d_od); cudaFree(x->d_oc); cudaFree(x->d_os);
     if (x->h_pin) cudaFreeHost(x->h_pin);
     if (x->scratch_free) cudaEventDestroy(x->scratch_free);
@@ -341,6 +343,7 @@ int gvss_reset(gvss_index *x) {
     free_device(x);
     x->h_keys.clear(); x->h_levels.clear(); x->h_upper_off.clear();
     x->entry = 0; x->max_level = -1; x->n_deleted = 0; x->lookup_valid = false; x->key_to_slot.clear(); x->free_slots.clear();
+    cudaMemset(x->d_build_stats, 0, 48);
     for (auto &v : x->st_vecs) v.clear();
     for (auto &v : x->st_keys) v.clear();
     x->st_device.clear(); x->st_device_rows.clear();
@@ -721,6 +724,18 @@ int gvss_get_info(gvss_index *x, gvss_info *out) {
     return 0;
 }
 
+int gvss_get_build_stats(gvss_index *x, gvss_build_stats *out) {
+    if (!x || !out) return fail("null argument");
+    std::lock_guard<std::mutex> lk(x->mu);
+    cudaSetDevice(x->device);
+    if (flush_locked(x)) return 1;
+    unsigned long long h[6] = {};
+    CU(cudaMemcpy(h, x->d_build_stats, sizeof h, cudaMemcpyDeviceToHost));
+    out->inserts = h[0]; out->query_distances = h[1]; out->pair_distances = h[2];
+    out->base_expansions = h[3]; out->upper_expansions = h[4]; out->rows_written = h[5];
+    return 0;
+}
+
 int gvss_get_level_stats(gvss_index *x, uint32_t level, gvss_level_stats *out) {
     if (!x || !out) return fail("null argument");
     std::lock_guard<std::mutex> lk(x->mu);
@@ -926,6 +941,7 @@ static int flush_locked(gvss_index *x) {
     unsigned long long *d_prof = nullptr;
     if (prof_on) { CU(prof_mem.alloc(d_prof, 8)); CU(cudaMemsetAsync(d_prof, 0, 64, x->stream)); }
     p.prof = d_prof;
+    p.stats = x->d_build_stats;
     // in-flight registry for the peer pass of k_build (GVSS_BUILD_PEERS=0 disables it)
     static const bool peers_on = [] { const char *e = getenv("GVSS_BUILD_PEERS"); return e ? atoi(e) != 0 : true; }();
     uint32_t *d_inflight = nullptr;

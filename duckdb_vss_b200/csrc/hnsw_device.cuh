@@ -103,6 +103,7 @@ struct WarpWs {
 #if GVSS_OPCOUNT
     unsigned long long opc[kOpCount];
 #endif
+    uint32_t n_pair, n_qdist, n_rows_written; // build statistics of this insert: node-to-node distances, extra query-to-node distances, adjacency rows written
     uint64_t *mbar;      // 2 mbarriers (one per stage buffer)
     uint32_t phase[2];
 };

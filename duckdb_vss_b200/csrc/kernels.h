@@ -72,6 +72,7 @@ struct BuildParams {
     uint32_t ef_add;
     int direct;
     uint32_t *inflight;       // [grid] slot each warp is inserting right now (kInvalid = idle); nullptr disables the peer pass
+    unsigned long long *stats; // [6] inserts, query distances, pair distances, level-0 expansions, upper expansions, rows written
     unsigned long long *prof; // optional phase clocks: [0] greedy [1] beam search [2] refine [3] connect [4] reconnect [5] inserts
     uint8_t *scratch;
     ScratchLayout sl;

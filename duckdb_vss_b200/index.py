@@ -154,6 +154,12 @@ class Index:
         capi.check(capi.lib().gvss_get_level_stats(self._h, int(level), C.byref(s)))
         return {f: getattr(s, f) for f, _ in capi.LevelStats._fields_}
 
+    def build_stats(self):
+        """Traversal counters summed over every insert (add_result_t::computed_distances / visited_members in bulk)."""
+        s = capi.BuildStats()
+        capi.check(capi.lib().gvss_get_build_stats(self._h, C.byref(s)))
+        return {f: getattr(s, f) for f, _ in capi.BuildStats._fields_}
+
 
 def exact_topk(metric, base, queries, k, keys=None):
     """Brute-force top-k with DuckDB's folds (array_kernels.hpp:11-105), ties by row index."""

@@ -151,6 +151,19 @@ int gvss_serialized_length(gvss_index *index, uint64_t *bytes);
 
 /* --- introspection ------------------------------------------------------------------------------------------- */
 int gvss_get_info(gvss_index *index, gvss_info *out);
+/* Traversal counters of the graph construction, summed over every insert since gvss_create / gvss_reset: the bulk form of
+ * add_result_t::computed_distances / visited_members (index.hpp:2133-2139), split the way SURVEY.md 8(d)'s build formula
+ * needs them: B_v = C_v*4d*w + H_v*(4+4*M0) + E_v*(4+4*M0). Flushes first. */
+typedef struct gvss_build_stats {
+    uint64_t inserts;             /* nodes linked into the graph */
+    uint64_t query_distances;     /* distances from the new vector to a node (one row read each, w = 1) */
+    uint64_t pair_distances;      /* node-to-node distances of the neighbour-selection heuristic and re-pruning (two rows, w = 2);
+                                     evaluated 32 candidates at a time: a few per cent above the reference's count on the same graph */
+    uint64_t base_expansions;     /* level-0 expansions of the insert-time beam searches (one adjacency row read each) */
+    uint64_t upper_expansions;    /* greedy hops and beam-search expansions on levels > 0 */
+    uint64_t rows_written;        /* adjacency rows written (own lists, appended and re-pruned reverse links) */
+} gvss_build_stats;
+int gvss_get_build_stats(gvss_index *index, gvss_build_stats *out);
 /* index.stats(level), hnsw_index.cpp:271-273 */
 int gvss_get_level_stats(gvss_index *index, uint32_t level, gvss_level_stats *out);
 

@@ -113,3 +113,31 @@ def test_sequential_gpu_build_long_rows_is_byte_identical(metric, d, n, M, check
     ix.add_batch(base)
     ix.flush()
     assert ix.save() == ref.save()
+
+
+def test_sequential_build_counters_equal_the_reference(checker):
+    """gvss_get_build_stats = add_result_t::computed_distances / visited_members (index.hpp:2133-2139) summed over the
+    adds: with one insert in flight the graph is the reference's byte for byte, and so are the traversal counters."""
+    Checker, kind = checker
+    if kind != "reference":
+        pytest.skip("per-add counters need the compiled reference")
+    n, d = 4000, 24
+    base, _ = synth.clustered(n, d, 40, 6, 77, 0)
+    ref = Checker(d, "l2sq", M=8, ef_construction=64)
+    ref.reserve(n, 1)
+    want = ref.add_bulk(base, threads=1)
+    ix = gv.Index(d, "l2sq", M=8, ef_construction=64)
+    ix.reserve(n, 1)
+    ix.set_build_concurrency(1)
+    ix.add_batch(base)
+    ix.flush()
+    assert ix.save() == ref.save()
+    st = ix.build_stats()
+    assert st["inserts"] == n - 1                      # the first node is placed without any search
+    assert st["base_expansions"] + st["upper_expansions"] == want["visited_members"]
+    # distance evaluations: the batched neighbour selection evaluates the 32 candidates of a window together, so the ones
+    # behind the candidate that fills the link list are measured although the reference's loop has stopped by then
+    # (same links, a few per cent more evaluations)
+    evaluated = st["query_distances"] + st["pair_distances"]
+    assert want["computed_distances"] <= evaluated <= 1.06 * want["computed_distances"]
+    assert st["rows_written"] >= n - 1
