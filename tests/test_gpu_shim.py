@@ -25,3 +25,16 @@ def test_shim_driver_behaves_like_the_reference_index(tmp_path):
     m = re.search(r"stream_bytes (\d+) serialized_length (\d+) load_ok 1 reloaded_size 728 same_results 1", out)
     assert m and m.group(1) == m.group(2)
     assert "after_reset_size 0" in out
+
+
+def test_multi_scan_prefetch_serves_the_index_join_from_one_batched_search(tmp_path):
+    """per-row ExecuteMultiScan loop vs the prefetching cache — identical ids for all 2048 outer rows."""
+    exe = str(tmp_path / "multiscan_driver")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", f"-I{ROOT}/include", f"-I{ROOT}/duckdb_vss_b200/shim",
+                    f"{ROOT}/tests/cpp/multiscan_driver.cpp", f"-L{libdir}", "-lgvss", f"-Wl,-rpath,{libdir}", "-o", exe], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True, timeout=300).stdout
+    print(out)
+    assert "prefetch_ok 1 served 2048/2048 same_ids 1 mismatched_counts 0 foreign 0 other_limit 0 after_reset 0" in out
+    m = re.search(r"speedup ([0-9.]+)", out)
+    assert m and float(m.group(1)) > 5.0  # one launch + one PCIe round trip instead of 2048
