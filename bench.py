@@ -46,6 +46,15 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def tensor_peak_tf32():
+    """Dense TF32 rate = half the dense bf16 rate; the bf16 figure is the measured one when the driver wrote it."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return float(j["bf16_tflops"]) / 2.0, "measured bf16 burst (MEASURED_PEAKS.json) / 2 for TF32"
+    return 2250.0 / 2.0, "fallback: nominal 2.25 PFLOP/s bf16 / 2 for TF32"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
 
@@ -418,6 +427,10 @@ def main():
                                    "frac": build_bytes / t_build / 1e9 / peak, "kernel": "k_build<l2sq>",
                                    "algorithmic_bytes": build_bytes, "note": "wall clock of the whole bulk build incl. uploads and the 16 ramp launches"}},
             "exact_topk": {"seconds": t_exact, "queries": nq, "base": n, "queries_per_s": nq / t_exact,
+                           "roofline": {"bound": "tensor", "achieved": 6.0 * nq * n * d / t_exact / 1e12, "peak": tensor_peak_tf32()[0],
+                                        "unit": "TFLOP/s", "frac": 6.0 * nq * n * d / t_exact / 1e12 / tensor_peak_tf32()[0],
+                                        "peak_source": tensor_peak_tf32()[1],
+                                        "note": "3xTF32: 3 tensor passes x 2*Q*N*d flops over the wall clock of the whole call (split, tiles, merge, re-rank)"},
                            "note": "ground truth: tcgen05 3xTF32 candidate tiles + exact re-rank (bit-exact vs DuckDB folds), 2nd call, wall clock incl. plane split"},
             "wall_s_timed_region": t_wall,
         }
