@@ -288,19 +288,50 @@ def main():
     st = ostat.cpu().numpy().view(np.uint32)
     algo_bytes = algorithmic_bytes(st, d, M, M0, k)
 
-    # multi-GPU exchange: all-gather of the per-shard lists (12*nq*k bytes per rank) + device merge
+    # multi-GPU exchange of the per-shard lists (12*nq*k bytes per rank) + device merge. Preferred: the merge kernel reads the
+    # peers' lists over NVLink out of symmetric memory and the ranks synchronise through flags in peer memory (no collective
+    # per step); fallback (GVSS_EXCHANGE=nccl, or symmetric memory unavailable): NCCL all-gather + merge of the gathered copy.
+    exchange, peer = "none", None
     if world > 1:
-        gk = torch.empty((world * nq, k), dtype=torch.int64, device=dev)   # rank-major [world][nq][k]
-        gd = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
         mk = torch.empty((nq, k), dtype=torch.int64, device=dev)
         md = torch.empty((nq, k), dtype=torch.float32, device=dev)
+        want_p2p = os.environ.get("GVSS_EXCHANGE", "p2p") != "nccl"
+        ok = torch.zeros(1, dtype=torch.int32, device=dev)
+        if want_p2p:
+            try:
+                from duckdb_vss_b200.sharded import PeerExchange
+                peer = PeerExchange(nq, k, dev)
+                ok += 1
+            except Exception as e:  # symmetric memory not available on this box / torch build
+                peer = None
+                if rank == 0:
+                    print(f"bench: peer-memory exchange unavailable ({e!r}); using NCCL all-gather", file=sys.stderr)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks or none
+        if int(ok.item()) == 0:
+            peer = None
+        exchange = "nvlink peer reads + flags in peer memory (k_merge_peers)" if peer else "nccl all_gather + k_merge"
+        if not peer:
+            gk = torch.empty((world * nq, k), dtype=torch.int64, device=dev)   # rank-major [world][nq][k]
+            gd = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
 
-    def step():
-        search(ef)
-        if world > 1:
+    def search_step():
+        if peer:
+            kp, dp = peer.outputs()
+            ix.search_device(q.data_ptr(), nq, k, ef, kp, dp, ocnt.data_ptr(), 0, stream)
+        else:
+            search(ef)
+
+    def exchange_step():
+        if peer:
+            peer.merge(mk, md)
+        elif world > 1:
             dist.all_gather_into_tensor(gk, okeys)
             dist.all_gather_into_tensor(gd, odist)
             gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, mk.data_ptr(), md.data_ptr(), stream)
+
+    def step():
+        search_step()
+        exchange_step()
 
     for _ in range(args.warmup):
         step()
@@ -315,12 +346,9 @@ def main():
         t_wall0 = time.perf_counter()
         for a, b, c in ev:
             a.record()
-            search(ef)
+            search_step()
             b.record()
-            if world > 1:
-                dist.all_gather_into_tensor(gk, okeys)
-                dist.all_gather_into_tensor(gd, odist)
-                gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, mk.data_ptr(), md.data_ptr(), stream)
+            exchange_step()
             c.record()
         torch.cuda.synchronize()
         t_wall = time.perf_counter() - t_wall0
@@ -334,7 +362,23 @@ def main():
         dist.barrier()
     merged_recall = None
     if world > 1:
+        # the merged list must contain this shard's own best hits wherever they beat the other shards'; and, when the
+        # peer-memory exchange is active, equal the result of the NCCL all-gather + merge path on the same inputs
         merged_recall = "n/a (per-shard ground truth only)"
+        if peer:
+            search_step()
+            exchange_step()
+            search(ef)
+            gk2 = torch.empty((world * nq, k), dtype=torch.int64, device=dev)
+            gd2 = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(gk2, okeys)
+            dist.all_gather_into_tensor(gd2, odist)
+            mk2, md2 = torch.empty_like(mk), torch.empty_like(md)
+            gv.merge_topk_device(gk2.data_ptr(), gd2.data_ptr(), world, nq, k, mk2.data_ptr(), md2.data_ptr(), stream)
+            torch.cuda.synchronize()
+            same = torch.tensor([int(torch.equal(mk, mk2) and torch.equal(md, md2))], dtype=torch.int32, device=dev)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            merged_recall = "peer-memory merge == nccl all_gather merge on all ranks" if int(same.item()) else "MISMATCH between peer-memory and nccl merge"
 
     # ---- e2e through the host-pointer C-ABI call (pinned host buffers; H2D + kernel + D2H inside the timed region) --
     qh = torch.from_numpy(q_np).pin_memory()
@@ -407,7 +451,8 @@ def main():
                        "units": "per-shard query searches summed over ranks (every query visits every shard)",
                        "global_queries_per_s": nq * args.steps / t_dev,
                        "l2_policy": "inputs larger than L2: 512 MB vectors + 128 MB adjacency per GPU vs 126 MB L2; no flush",
-                       "parallelism": f"shard{world}" if world > 1 else "single"},
+                       "parallelism": f"shard{world}" if world > 1 else "single", "exchange": exchange,
+                       "exchange_check": merged_recall},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel": "k_search<l2sq>",
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": 1e3 * t_kernel},

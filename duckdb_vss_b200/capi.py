@@ -71,6 +71,8 @@ SIGNATURES = {
                                          C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gvss_merge_topk_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p,
                                          C.c_void_p, C.c_void_p]),
+    "gvss_merge_topk_peers_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                               C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gvss_set_build_concurrency": (C.c_int, [C.c_void_p, C.c_uint32]),
     "gvss_last_error": (C.c_char_p, []),
     "gvss_version": (C.c_char_p, []),

@@ -180,46 +180,97 @@ __global__ void __launch_bounds__(kRows) k_exact(const float *__restrict__ base,
 // MODE 0: inputs are (order-key|row, dist) partials of k_exact (unique keys; row -> optional keys[] lookup)
 // MODE 1: inputs are (key i64, dist) lists from different GPUs; order (dist, key), padding entries (key -1) last
 template <int MODE>
+__device__ __forceinline__ void merge_entry(const unsigned long long *__restrict__ in_key, const float *__restrict__ in_dist, uint64_t nq,
+                                            uint64_t q, uint32_t k, uint32_t e, unsigned long long &hi, unsigned long long &lo, float &dv) {
+    const uint32_t s = e / k, i = e % k;
+    const size_t o = ((size_t)s * nq + q) * k + i;
+    dv = in_dist[o];
+    if (MODE == 0) { hi = in_key[o]; lo = e; }
+    else {
+        const long long key = (long long)in_key[o];
+        const bool pad = key < 0 && !(dv < CUDART_INF_F);
+        hi = ((unsigned long long)(pad ? 0xFFFFFFFFu : order_key(dv)) << 32) | (pad ? 0xFFFFFFFFu : 0u);
+        lo = (unsigned long long)key ^ 0x8000000000000000ull; // signed order; (dist, key) lexicographic
+    }
+}
+
+// STAGED: the query's shards*k sort keys are staged in shared memory once (16 B each) and every lane ranks its own
+// elements (held in registers, at most kMergePerLane) against one broadcast element per step; otherwise (lists too long
+// for shared memory) every comparison re-reads global memory.
+constexpr uint32_t kMergePerLane = 16;
+template <int MODE, bool STAGED>
 __global__ void k_merge(const unsigned long long *__restrict__ in_key, const float *__restrict__ in_dist, uint32_t shards,
                         uint64_t nq, uint32_t k, const int64_t *__restrict__ id_map, int64_t *__restrict__ keys_out,
                         float *__restrict__ dist_out) {
+    extern __shared__ __align__(16) unsigned long long merge_smem[];
     const uint64_t q = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
     if (q >= nq) return;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t total = shards * k;
-    auto get = [&](uint32_t e, unsigned long long &hi, unsigned long long &lo, float &dv) {
-        const uint32_t s = e / k, i = e % k;
-        const size_t o = ((size_t)s * nq + q) * k + i;
-        dv = in_dist[o];
-        if (MODE == 0) { hi = in_key[o]; lo = e; }
-        else {
-            const long long key = (long long)in_key[o];
-            const bool pad = key < 0 && !(dv < CUDART_INF_F);
-            hi = ((unsigned long long)(pad ? 0xFFFFFFFFu : order_key(dv)) << 32) | (pad ? 0xFFFFFFFFu : 0u);
-            lo = (unsigned long long)key ^ 0x8000000000000000ull; // signed order
-            hi |= 0; // (dist, key) lexicographic; equal pairs cannot occur for disjoint shards
-        }
+    auto emit = [&](uint32_t e, uint32_t rank, float dv) {
+        if (rank >= k) return;
+        const unsigned long long kk = in_key[((size_t)(e / k) * nq + q) * k + (e % k)];
+        int64_t id;
+        if (MODE == 0) {
+            if (kk == ~0ull) id = -1;
+            else { const uint32_t row = (uint32_t)(kk & 0xFFFFFFFFull); id = id_map ? id_map[row] : (int64_t)row; }
+        } else id = (int64_t)kk;
+        keys_out[q * k + rank] = id;
+        if (dist_out) dist_out[q * k + rank] = dv;
     };
+    if (STAGED) {
+        unsigned long long *sh = merge_smem + (size_t)(threadIdx.x >> 5) * total * 2; // (hi, lo) pairs
+        unsigned long long mhi[kMergePerLane], mlo[kMergePerLane];
+        float mdv[kMergePerLane];
+        uint32_t rank[kMergePerLane];
+#pragma unroll
+        for (uint32_t j = 0; j < kMergePerLane; j++) {
+            const uint32_t e = lane + 32 * j;
+            rank[j] = 0;
+            mhi[j] = ~0ull; mlo[j] = ~0ull; mdv[j] = 0.f;
+            if (e < total) {
+                merge_entry<MODE>(in_key, in_dist, nq, q, k, e, mhi[j], mlo[j], mdv[j]);
+                sh[2 * e] = mhi[j];
+                sh[2 * e + 1] = mlo[j];
+            }
+        }
+        __syncwarp();
+        for (uint32_t o = 0; o < total; o++) {
+            const ulonglong2 x = *reinterpret_cast<const ulonglong2 *>(sh + 2 * o); // broadcast
+#pragma unroll
+            for (uint32_t j = 0; j < kMergePerLane; j++) {
+                const uint32_t e = lane + 32 * j;
+                rank[j] += (x.x < mhi[j] || (x.x == mhi[j] && (x.y < mlo[j] || (x.y == mlo[j] && o < e)))) ? 1u : 0u;
+            }
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < kMergePerLane; j++)
+            if (lane + 32 * j < total) emit(lane + 32 * j, rank[j], mdv[j]);
+        return;
+    }
     for (uint32_t e = lane; e < total; e += 32) {
         unsigned long long hi, lo; float dv;
-        get(e, hi, lo, dv);
+        merge_entry<MODE>(in_key, in_dist, nq, q, k, e, hi, lo, dv);
         uint32_t rank = 0;
         for (uint32_t o = 0; o < total; o++) {
             unsigned long long h2, l2; float d2;
-            get(o, h2, l2, d2);
+            merge_entry<MODE>(in_key, in_dist, nq, q, k, o, h2, l2, d2);
             rank += (h2 < hi || (h2 == hi && (l2 < lo || (l2 == lo && o < e)))) ? 1u : 0u;
         }
-        if (rank < k) {
-            int64_t id;
-            if (MODE == 0) {
-                const unsigned long long kk = in_key[((size_t)(e / k) * nq + q) * k + (e % k)];
-                if (kk == ~0ull) id = -1;
-                else { const uint32_t row = (uint32_t)(kk & 0xFFFFFFFFull); id = id_map ? id_map[row] : (int64_t)row; }
-            } else id = (int64_t)in_key[((size_t)(e / k) * nq + q) * k + (e % k)];
-            keys_out[q * k + rank] = id;
-            if (dist_out) dist_out[q * k + rank] = dv;
-        }
+        emit(e, rank, dv);
     }
+}
+
+template <int MODE>
+static cudaError_t launch_merge(const unsigned long long *in_key, const float *in_dist, uint32_t shards, uint64_t nq, uint32_t k,
+                                const int64_t *id_map, int64_t *keys_out, float *dist_out, cudaStream_t st) {
+    const uint32_t wpb = 4, total = shards * k;
+    const unsigned grid = (unsigned)((nq + wpb - 1) / wpb);
+    const size_t smem = (size_t)wpb * total * 16;
+    if (total <= 32 * kMergePerLane && smem <= 48 * 1024) k_merge<MODE, true><<<grid, wpb * 32, smem, st>>>(in_key, in_dist, shards, nq, k, id_map, keys_out, dist_out);
+    else k_merge<MODE, false><<<grid, wpb * 32, 0, st>>>(in_key, in_dist, shards, nq, k, id_map, keys_out, dist_out);
+    count_launch();
+    return cudaGetLastError();
 }
 
 template <char METRIC, int QT>
@@ -249,10 +300,7 @@ static cudaError_t run_exact(const float *base, uint64_t n, const int64_t *keys,
     dim3 grid((unsigned)qtiles, (unsigned)splits);
     k_exact<METRIC, QT><<<grid, kRows, smem, st>>>(base, n, queries, nq, d, k, rows_per_split, pk, pd);
     count_launch();
-    const uint32_t wpb = 4;
-    k_merge<0><<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(pk, pd, (uint32_t)splits, nq, k, keys, ids_out, dist_out);
-    count_launch();
-    e = cudaGetLastError();
+    e = launch_merge<0>(pk, pd, (uint32_t)splits, nq, k, keys, ids_out, dist_out, st);
     cudaFreeAsync(pk, st);
     cudaFreeAsync(pd, st);
     return e;
@@ -272,10 +320,7 @@ cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const 
 cudaError_t launch_merge_partials(const unsigned long long *pk, const float *ps, uint32_t splits, uint64_t nq, uint32_t kc, int64_t *rows_out,
                                   float *scores_out, cudaStream_t st) {
     if (!nq) return cudaSuccess;
-    const uint32_t wpb = 4;
-    k_merge<0><<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(pk, ps, splits, nq, kc, nullptr, rows_out, scores_out);
-    count_launch();
-    return cudaGetLastError();
+    return launch_merge<0>(pk, ps, splits, nq, kc, nullptr, rows_out, scores_out, st);
 }
 
 __global__ void k_gather_rows(const float *__restrict__ src, const uint32_t *__restrict__ idx, uint64_t m, uint32_t d, float *__restrict__ dst) {
@@ -326,9 +371,121 @@ cudaError_t launch_exact_topk_flagged(char metric, const float *base, uint64_t n
 cudaError_t launch_merge_topk(const int64_t *gk, const float *gd, uint32_t shards, uint64_t nq, uint32_t k, int64_t *keys_out,
                               float *dist_out, cudaStream_t st) {
     if (!nq) return cudaSuccess;
+    return launch_merge<1>(reinterpret_cast<const unsigned long long *>(gk), gd, shards, nq, k, nullptr, keys_out, dist_out, st);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Multi-GPU exchange without a collective library: every rank's merge kernel reads the peers' per-shard lists straight
+// out of THEIR memory over NVLink (the host maps the peers' buffers into this process, e.g. through CUDA IPC / symmetric
+// memory) and the ranks synchronise through one 32-bit flag per (reader, writer) pair:
+//   1. this kernel follows the rank's own search in stream order, so when it starts the rank's lists are complete; CTA 0
+//      publishes `step` into slot [rank] of every peer's flag array (release, system scope);
+//   2. every warp waits until all slots of its OWN flag array have reached `step` (acquire, system scope) — the peers' lists
+//      of this step are then complete and visible;
+//   3. the lists are merged by (distance, key) like k_merge<1>.
+// Steps must increase by one per call on every rank and result buffers must be double-buffered by the caller (a rank may
+// start step s+1's search while a slow peer still merges step s). A peer that never arrives trips the time-out and the
+// kernel traps instead of hanging the GPU.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t kMaxPeers = 16;
+struct PeerLists {
+    const unsigned long long *keys[kMaxPeers];
+    const float *dist[kMaxPeers];
+    uint32_t *flags[kMaxPeers]; // flags[r] = rank r's flag array (kMaxPeers u32), mapped here
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_relaxed_sys_f32(const float *p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void k_merge_peers(PeerLists pl, uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k,
+                              int64_t *__restrict__ keys_out, float *__restrict__ dist_out) {
+    const uint32_t lane = threadIdx.x & 31u;
+    if (blockIdx.x == 0 && threadIdx.x < shards) {
+        __threadfence_system();
+        st_release_sys(pl.flags[threadIdx.x] + rank, step);
+    }
+    if (lane < shards) {
+        const uint32_t *mine = pl.flags[rank] + lane;
+        const long long t0 = clock64();
+        // wrap-safe "reached step"; ~4 s at 2 GHz before giving up
+        while ((int32_t)(ld_acquire_sys(mine) - step) < 0) {
+            if (clock64() - t0 > 8000000000ll) { printf("k_merge_peers: rank %u timed out waiting for rank %u at step %u\n", rank, lane, step); __trap(); }
+            __nanosleep(200);
+        }
+    }
+    __syncwarp();
+    const uint64_t q = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const uint32_t total = shards * k;
+    auto get = [&](uint32_t e, unsigned long long &hi, unsigned long long &lo, float &dv, long long &key) {
+        const uint32_t s = e / k, i = e % k;
+        key = (long long)ld_relaxed_sys_u64(pl.keys[s] + q * k + i);
+        dv = ld_relaxed_sys_f32(pl.dist[s] + q * k + i);
+        const bool pad = key < 0 && !(dv < CUDART_INF_F);
+        hi = ((unsigned long long)(pad ? 0xFFFFFFFFu : order_key(dv)) << 32) | (pad ? 0xFFFFFFFFu : 0u);
+        lo = (unsigned long long)key ^ 0x8000000000000000ull;
+    };
+    // each lane owns up to 8 elements (shards * k <= 256); the others are broadcast from the owners' registers
+    unsigned long long mhi[8], mlo[8];
+    float mdv[8];
+    long long mkey[8];
+    uint32_t rk[8];
+#pragma unroll
+    for (uint32_t j = 0; j < 8; j++) {
+        rk[j] = 0; mhi[j] = ~0ull; mlo[j] = ~0ull; mdv[j] = 0.f; mkey[j] = -1;
+        if (lane + 32 * j < total) get(lane + 32 * j, mhi[j], mlo[j], mdv[j], mkey[j]);
+    }
+#pragma unroll
+    for (uint32_t jo = 0; jo < 8; jo++) {
+        if (jo * 32 >= total) break;
+        for (uint32_t src = 0; src < 32 && jo * 32 + src < total; src++) {
+            const unsigned long long xh = __shfl_sync(kFull, mhi[jo], src), xl = __shfl_sync(kFull, mlo[jo], src);
+            const uint32_t o = jo * 32 + src;
+#pragma unroll
+            for (uint32_t j = 0; j < 8; j++) {
+                const uint32_t e = lane + 32 * j;
+                rk[j] += (xh < mhi[j] || (xh == mhi[j] && (xl < mlo[j] || (xl == mlo[j] && o < e)))) ? 1u : 0u;
+            }
+        }
+    }
+#pragma unroll
+    for (uint32_t j = 0; j < 8; j++) {
+        if (lane + 32 * j < total && rk[j] < k) {
+            keys_out[q * k + rk[j]] = mkey[j];
+            if (dist_out) dist_out[q * k + rk[j]] = mdv[j];
+        }
+    }
+}
+
+cudaError_t launch_merge_topk_peers(const int64_t *const *peer_keys, const float *const *peer_dist, uint32_t *const *peer_flags,
+                                    uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k, int64_t *keys_out,
+                                    float *dist_out, cudaStream_t st) {
+    if (!shards || shards > kMaxPeers || rank >= shards || (uint64_t)shards * k > 256) return cudaErrorInvalidValue;
+    PeerLists pl{};
+    for (uint32_t s = 0; s < shards; s++) {
+        pl.keys[s] = reinterpret_cast<const unsigned long long *>(peer_keys[s]);
+        pl.dist[s] = peer_dist[s];
+        pl.flags[s] = peer_flags[s];
+    }
     const uint32_t wpb = 4;
-    k_merge<1><<<(unsigned)((nq + wpb - 1) / wpb), wpb * 32, 0, st>>>(reinterpret_cast<const unsigned long long *>(gk), gd, shards, nq,
-                                                                      k, nullptr, keys_out, dist_out);
+    const unsigned grid = (unsigned)(((nq ? nq : 1) + wpb - 1) / wpb); // at least CTA 0: the flags must be published even for an empty batch
+    k_merge_peers<<<grid, wpb * 32, 0, st>>>(pl, rank, shards, step, nq, k, keys_out, dist_out);
     count_launch();
     return cudaGetLastError();
 }

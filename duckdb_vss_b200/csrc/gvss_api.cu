@@ -767,6 +767,18 @@ int gvss_merge_topk_device(const int64_t *gk, const float *gd, uint32_t shards, 
     return 0;
 }
 
+int gvss_merge_topk_peers_device(const int64_t *const *peer_keys, const float *const *peer_dist, uint32_t *const *peer_flags,
+                                 uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k, int64_t *keys_out,
+                                 float *dist_out, void *cuda_stream) {
+    if (!peer_keys || !peer_dist || !peer_flags || !keys_out) return fail("gvss_merge_topk_peers_device: null buffer");
+    if (!shards || shards > 16 || rank >= shards) return fail("gvss_merge_topk_peers_device: 1..16 shards, rank < shards");
+    if ((uint64_t)shards * k > 256) return fail("gvss_merge_topk_peers_device: shards * k must not exceed 256");
+    for (uint32_t s = 0; s < shards; s++)
+        if (!peer_keys[s] || !peer_dist[s] || !peer_flags[s]) return fail("gvss_merge_topk_peers_device: null peer pointer (shard %u)", s);
+    CU(launch_merge_topk_peers(peer_keys, peer_dist, peer_flags, rank, shards, step, nq, k, keys_out, dist_out, (cudaStream_t)cuda_stream));
+    return 0;
+}
+
 int gvss_exact_topk_device(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries, uint64_t nq,
                            uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out, void *cuda_stream) {
     if (!base || !queries || !ids_out) return fail("gvss_exact_topk_device: null buffer");

@@ -80,6 +80,10 @@ struct BuildParams {
 };
 cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t stream);
 
+// multi-GPU merge that reads the peers' lists over NVLink and synchronises through flags in peer memory (exact.cu)
+cudaError_t launch_merge_topk_peers(const int64_t *const *peer_keys, const float *const *peer_dist, uint32_t *const *peer_flags,
+                                    uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k, int64_t *keys_out,
+                                    float *dist_out, cudaStream_t stream);
 cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries,
                               uint64_t nq, uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out,
                               cudaStream_t stream);

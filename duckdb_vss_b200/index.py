@@ -184,3 +184,13 @@ def merge_topk_device(keys_ptr, dist_ptr, shards, nq, k, out_keys_ptr, out_dist_
     capi.check(capi.lib().gvss_merge_topk_device(C.c_void_p(keys_ptr), C.c_void_p(dist_ptr), int(shards), int(nq),
                                                  int(k), C.c_void_p(out_keys_ptr), C.c_void_p(out_dist_ptr),
                                                  C.c_void_p(stream or None)))
+
+
+def merge_topk_peers_device(peer_keys, peer_dist, peer_flags, rank, step, nq, k, out_keys_ptr, out_dist_ptr, stream=0):
+    """Merge that reads the peers' lists over NVLink (gvss_merge_topk_peers_device). peer_*: sequences of device
+    pointers (ints), one per shard, as mapped into this process."""
+    shards = len(peer_keys)
+    arr = C.c_void_p * shards
+    capi.check(capi.lib().gvss_merge_topk_peers_device(arr(*peer_keys), arr(*peer_dist), arr(*peer_flags), int(rank), shards,
+                                                       int(step), int(nq), int(k), C.c_void_p(out_keys_ptr),
+                                                       C.c_void_p(out_dist_ptr or None), C.c_void_p(stream or None)))

@@ -183,6 +183,17 @@ int gvss_exact_topk_device(char metric, const float *base, uint64_t n, const int
 int gvss_merge_topk_device(const int64_t *gathered_keys, const float *gathered_dist, uint32_t shards, uint64_t nq,
                            uint32_t k, int64_t *keys_out, float *dist_out, void *cuda_stream);
 
+/* The same merge WITHOUT a preceding all-gather: the kernel reads every shard's nq×k list out of the owning GPU's memory
+ * over NVLink and the ranks synchronise through flags in peer memory (no reference counterpart).
+ * peer_keys[s] / peer_dist[s]: shard s's result buffers as mapped into THIS process (CUDA IPC / symmetric memory; entry
+ * [rank] is the local buffer); peer_flags[s]: shard s's flag array (16 zero-initialised u32). All three are HOST arrays
+ * of `shards` device pointers. Call it on every rank, after that rank's search on the same stream, with the same `step`
+ * = 1, 2, 3, ... ; the caller alternates between two sets of result buffers from step to step. shards <= 16,
+ * shards * k <= 256. A rank that never arrives makes the others trap after ~4 s instead of hanging. */
+int gvss_merge_topk_peers_device(const int64_t *const *peer_keys, const float *const *peer_dist, uint32_t *const *peer_flags,
+                                 uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k, int64_t *keys_out,
+                                 float *dist_out, void *cuda_stream);
+
 /* --- misc ---------------------------------------------------------------------------------------------------- */
 const char *gvss_last_error(void);
 const char *gvss_version(void);

@@ -130,3 +130,34 @@ def test_tensor_core_path_falls_back_on_ties_it_cannot_resolve():
     np.testing.assert_array_equal(ids, want_ids)
     np.testing.assert_array_equal(dist.view(np.uint32), want_d.view(np.uint32))
     assert flagged >= 1
+
+
+def test_peer_merge_kernel_equals_gathered_merge_single_process():
+    """gvss_merge_topk_peers_device with both 'peers' in this process (flags pre-set, so nobody waits): same output as
+    gvss_merge_topk_device on the gathered copy. The cross-process use (symmetric memory, one flag per pair of ranks)
+    is exercised by bench.py --gpus N."""
+    import torch
+    from duckdb_vss_b200 import index as gvi
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(3)
+    shards, nq, k = 3, 500, 10
+    d = np.sort(rng.random((shards, nq, k), dtype=np.float32), axis=2)
+    d[1, :, 7:] = np.inf                                    # short lists: padding (key -1, +inf)
+    keys = rng.permutation(shards * nq * k).astype(np.int64).reshape(shards, nq, k)
+    keys[1, :, 7:] = -1
+    d[2, :, 0] = d[0, :, 0]                                 # exact distance ties across shards: ordered by key
+    gk, gd = torch.from_numpy(keys).to(dev), torch.from_numpy(d).to(dev)
+    want_k = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    want_d = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    gvi.merge_topk_device(gk.data_ptr(), gd.data_ptr(), shards, nq, k, want_k.data_ptr(), want_d.data_ptr())
+    flags = [torch.full((16,), 5, dtype=torch.int32, device=dev) for _ in range(shards)]
+    got_k, got_d = torch.empty_like(want_k), torch.empty_like(want_d)
+    for rank in range(shards):
+        got_k.fill_(-7)
+        gvi.merge_topk_peers_device([gk[s].data_ptr() for s in range(shards)], [gd[s].data_ptr() for s in range(shards)],
+                                    [f.data_ptr() for f in flags], rank, 5, nq, k, got_k.data_ptr(), got_d.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.equal(got_k, want_k) and torch.equal(got_d, want_d)
+    with pytest.raises(gv.GvssError, match="256"):
+        gvi.merge_topk_peers_device([gk.data_ptr()] * 16, [gd.data_ptr()] * 16, [flags[0].data_ptr()] * 16, 0, 6, nq, 32,
+                                    got_k.data_ptr(), got_d.data_ptr())
