@@ -1,16 +1,21 @@
 // Warp-level device primitives of the HNSW hot path (sm_100a). One warp owns one query / one insert.
 //
 // Numerics contract: every distance is a strict left-to-right fp32 sum with separate multiply and add
-// (__fmul_rn/__fadd_rn, never contracted into FMA) computed by ONE lane over a whole row, so its bits equal
-// the reference's scalar loops on x86-64 (usearch index_plugins.hpp:981-993 ip, :1006-1026 cos, :1037-1052 l2sq).
-// Rows are brought from HBM into shared memory by TMA bulk copies (cp.async.bulk, 16-byte granules, mbarrier
-// completion) — or, with WarpWs::use_tma off (GVSS_USE_TMA=0), by coalesced 16-byte cp.async — into a padded layout
-// that makes the per-lane float4 reads bank-conflict free; 32 neighbours are evaluated at once, lane i <-> row i.
+// (__fmul_rn/__fadd_rn or the packed sub.rn.f32x2 / mul.rn.f32x2, never contracted into FMA) computed by ONE lane over a
+// whole row, so its bits equal the reference's scalar loops on x86-64 (usearch index_plugins.hpp:981-993 ip, :1006-1026
+// cos, :1037-1052 l2sq). Rows are brought from HBM into shared memory by TMA, completion on an mbarrier:
+//   * search: warp_distances_g4 — cp.async.bulk.tensor ... tile::gather4 (one instruction = the same 128-byte line of four
+//     arbitrary rows) into a 128-byte-swizzled 4 KB stage; lane i <-> row i for all 32 lanes;
+//   * build (and GVSS_GATHER4=0): warp_distances — one 1-D bulk copy (cp.async.bulk) per row chunk into rows with an odd
+//     number of 16-byte granules; coalesced 16-byte cp.async with GVSS_USE_TMA=0 (A/B only).
+// Both layouts make the per-lane LDS.128 reads bank-conflict free.
 //
-// Control flow contract: the candidate queue (`next`), the result list (`top`) and the acceptance test replay
-// usearch's containers operation by operation (index.hpp:516-645 max_heap_gt, :655-766 sorted_buffer_gt,
-// :3504-3573 search_to_find_in_base_, :3430-3496 search_to_insert_), so results, their order among ties and the
-// traversal counters are identical to the reference on the same graph.
+// Control flow contract (beam_search): the result list (`top`) is usearch's sorted buffer (index.hpp:655-766) and the
+// acceptance test replays search_to_find_in_base_ / search_to_insert_ (:3504-3573, :3430-3496) for a whole batch of
+// neighbours at once. The candidate queue (`next`, max_heap_gt :516-645) is not materialised on the fast path: the result
+// list doubles as the queue, and usearch's binary heap is rebuilt from a log of the queue operations only when two live
+// candidates tie exactly for the head of the queue. Results, their order among ties and the traversal counters are
+// identical to the reference on the same graph.
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
