@@ -940,8 +940,10 @@ static int flush_locked(gvss_index *x) {
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
     p.sl = make_scratch_layout(std::max(p.ef_add, cmax), next_fresh, cmax);
     static const uint32_t build_rows = [] { const char *e = getenv("GVSS_BUILD_STAGE_ROWS"); const uint32_t v = e ? (uint32_t)atoi(e) : 32u; return v == 16u ? 16u : 32u; }();
-    p.sm = make_smem_layout(x->dpad, top_cap, default_heap_smem(p.ef_add), (2 * cmax + 2) * 8, build_rows, true, cmax);
     p.direct = search_mode_bits();
+    // with the list-as-queue beam search the heap only serves exact ties: 32 entries (its 5 top levels) stay in shared memory
+    const uint32_t build_heap = (p.direct & 8) ? default_heap_smem(p.ef_add) : 32u;
+    p.sm = make_smem_layout(x->dpad, top_cap, build_heap, (2 * cmax + 2) * 8, build_rows, true, cmax);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
     if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) return 1;

@@ -133,7 +133,7 @@ SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem,
     s.off_mbar = take(16, 16);
     if (!gather4) s.off_stage0 = take(stage_bytes, 128);
     s.off_stage1 = two ? take(stage_bytes, 128) : s.off_stage0;
-    s.off_c = take(with_left ? 2 * kChunk * 4 : 0, 128);
+    s.off_c = take(with_left ? (two ? 2u : 1u) * kChunk * 4 : 0, 128); // streamed left-hand chunk, double-buffered with the stage
     s.off_q = take(dpad * 4, 16);
     s.heap_smem = heap_smem;
     s.off_heap = take(heap_smem * 8, 16);

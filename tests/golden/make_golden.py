@@ -1,7 +1,7 @@
 """Regenerates the golden fixtures in this directory from the COMPILED REFERENCE (oracle/_ref, i.e. the unmodified
 vendored usearch + DuckDB array kernels under /root/reference). Run in the build container only:
 
-    python tests/golden/make_golden.py
+    python tests/golden/make_golden.py [case ...]
 
 Fixtures (all small):
   <name>.usearch   — stream written by the reference's save_to_stream after a single-thread build
@@ -30,8 +30,13 @@ CASES["clustered24_cos"] = ("cosine", b, q, 8, 0, 64)
 b, q = synth.clustered(900, 12, 16, 4, 13, 40)
 b /= np.linalg.norm(b, axis=1, keepdims=True)
 CASES["clustered12_ip"] = ("ip", b, q, 4, 6, 40)
+b, q = synth.clustered(1000, 40, 20, 8, 14, 40)  # rows longer than one 128-byte line (second line partial): the GPU's gather4 staging path
+CASES["clustered40_l2sq"] = ("l2sq", b, q, 16, 0, 128)
+only = set(sys.argv[1:])  # optional: regenerate only the named cases
 
 for name, (metric, base, queries, M, M0, efc) in CASES.items():
+    if only and name not in only:
+        continue
     ix = ref.RefIndex(base.shape[1], metric, M=M, M0=M0, ef_construction=efc)
     ix.reserve(base.shape[0], 1)
     ix.add_bulk(base, threads=1)
