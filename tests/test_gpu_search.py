@@ -100,6 +100,26 @@ def test_tie_heavy_integer_data_matches_reference_pop_order(metric, d, n, levels
     assert tied > 300  # the tie path really ran (3 x 200 queries)
 
 
+@pytest.mark.parametrize("n,d", [(40, 40), (7, 128), (1, 32), (33, 8)])
+def test_graph_smaller_than_the_beam(n, d, checker):
+    """ef larger than the whole graph: the result list never fills, the search ends when every member is expanded."""
+    Checker, kind = checker
+    base, q = synth.clustered(n, d, 4, 3, 900 + n, 25)
+    ref = Checker(d, "l2sq", M=4)
+    ref.reserve(n, 1)
+    ref.add_bulk(base, threads=1)
+    ix = gv.Index(d, "l2sq", M=4)
+    ix.load(ref.save())
+    for ef in (3, 64):
+        want = ref.search_batch(q, 10, ef)
+        keys, dist, counts, st = ix.ef_search(q, 10, ef, stats=True)
+        np.testing.assert_array_equal(keys, want["keys"], err_msg=f"n={n} d={d} ef={ef} ({kind})")
+        np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32))
+        np.testing.assert_array_equal(counts, want["counts"])
+        np.testing.assert_array_equal(st["computed"], want["computed"].astype(np.uint32))
+        np.testing.assert_array_equal(st["visited"], want["visited"].astype(np.uint32))
+
+
 def test_removed_members_are_traversed_but_never_returned(checker):
     Checker, _ = checker
     n, d = 3000, 16
