@@ -17,6 +17,7 @@ __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, cons
                                             const ScratchLayout &sl, int direct) {
     w.g4 = false; // the build stages whole rows (neighbour selection re-reads them); gather4 staging is a search path
     w.vmap = nullptr;
+    w.q_a2 = 0.0f;
     w.prefetch_rows = false;
     w.prefetch_vis = (direct & 64) == 0;
     w.direct = (direct & 1) != 0;

@@ -91,6 +91,7 @@ struct WarpWs {
     bool direct;         // query-to-node distances stream each lane's row straight into registers (no staging)
     bool g4;             // query-to-node distances stage 32 rows x 32 floats per step by TMA gather4 (stage[0]: 4 KB, 1024-aligned)
     const CUtensorMap *vmap; // ... through this 2-D map over `vectors`
+    float q_a2;          // cosine, g4: sum of squares of the query, folded once per query in the reference's order (identical bits)
     bool prefetch_rows;  // g4: L2 prefetch of every line of every new row at the start of a hop
     bool prefetch_vis;   // L2 prefetch of the visited windows of neighbours 32.. while neighbours 0..31 are tested
     uint32_t *nb;        // new (unvisited) neighbours of the node being expanded, in list order
@@ -243,6 +244,27 @@ template <int METRIC> __device__ __forceinline__ void acc_pair(Acc &r, float2 a,
         }
     }
 }
+// cosine with a known left-hand norm: only ab and b2 are folded per row (the reference recomputes a2 for every row, always
+// from the same query in the same order, so the value cached in WarpWs::q_a2 has the same bits)
+template <int METRIC, bool SKIP_A2> __device__ __forceinline__ void acc_pair_q(Acc &r, float2 a, float2 b) {
+    if (METRIC == kCos && SKIP_A2) {
+        const float2 p = mul2(a, b), pb = mul2(b, b);
+        r.ab = __fadd_rn(__fadd_rn(r.ab, p.x), p.y);
+        r.b2 = __fadd_rn(__fadd_rn(r.b2, pb.x), pb.y);
+    } else acc_pair<METRIC>(r, a, b);
+}
+// left-hand norm of a vector in shared memory, folded exactly as acc_pair<kCos> folds a2 (lane 0 computes, all lanes get it)
+__device__ __forceinline__ float fold_a2(const float *v, uint32_t n) {
+    float a2 = 0.0f;
+    if (lane_id() == 0) {
+        for (uint32_t i = 0; i < n; i += 2) {
+            const float2 x = make_float2(v[i], v[i + 1]);
+            const float2 p = mul2(x, x);
+            a2 = __fadd_rn(__fadd_rn(a2, p.x), p.y);
+        }
+    }
+    return __shfl_sync(kFull, a2, 0);
+}
 // d(query in shared memory, row `my_slot`) for every active lane; dpad is a multiple of 8 floats
 template <int METRIC>
 __device__ __noinline__ float direct_distance(const float *vectors, uint32_t dpad, const float *qs, uint32_t my_slot, bool active) {
@@ -318,14 +340,14 @@ __device__ __forceinline__ float warp_distances_g4(const GraphView &g, WarpWs &w
 #pragma unroll
                     for (uint32_t i = 0; i < kG4Chunk / 4; i++) {
                         const float4 x = a[i], y = myrow[i ^ sw];
-                        acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
-                        acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                        acc_pair_q<METRIC, true>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
+                        acc_pair_q<METRIC, true>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
                     }
                 } else {
                     for (uint32_t i = 0; i < nfl / 4; i++) {
                         const float4 x = a[i], y = myrow[i ^ sw];
-                        acc_pair<METRIC>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
-                        acc_pair<METRIC>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
+                        acc_pair_q<METRIC, true>(acc, make_float2(x.x, x.y), make_float2(y.x, y.y));
+                        acc_pair_q<METRIC, true>(acc, make_float2(x.z, x.w), make_float2(y.z, y.w));
                     }
                 }
             }
@@ -334,6 +356,7 @@ __device__ __forceinline__ float warp_distances_g4(const GraphView &g, WarpWs &w
         OPCLK(t3);
         OPC(kOpClkStage, t1 - t0); OPC(kOpClkWait, t2 - t1); OPC(kOpClkMath, t3 - t2); OPC(kOpSteps, 1);
     }
+    if (METRIC == kCos) acc.a2 = w.q_a2;
     return active ? acc_finish<METRIC>(acc) : 0.0f;
 }
 

@@ -68,6 +68,7 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         const float *qsrc = p.queries + qi * g.dims;
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = i < g.dims ? __ldg(qsrc + i) : 0.0f;
         __syncwarp();
+        if (METRIC == kCos && w.g4) w.q_a2 = fold_a2(w.q, g.dpad);
 
         Counters cnt = {0, 0, 0, (long long)qi == p.trace_query ? 0x80000000u : 0u};
         uint32_t top_size = 0;
