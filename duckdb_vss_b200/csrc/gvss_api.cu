@@ -893,23 +893,42 @@ static int flush_locked(gvss_index *x) {
 
     // 2. upload rows (16-byte padded), keys, levels, upper offsets; reset lists of recycled nodes
     if (!host_rows.empty()) {
-        const size_t need = host_rows.size() * (size_t)x->dpad * 4;
+        // staged host rows go up through two pinned bounce buffers: while one chunk is on its way to the GPU the next one is
+        // padded into the other buffer (no pinned allocation of the size of the whole batch, copy and padding overlap)
+        const size_t row_bytes = (size_t)x->dpad * 4;
+        size_t chunk_rows = (16u << 20) / row_bytes;
+        if (chunk_rows < 1) chunk_rows = 1;
+        if (chunk_rows > host_rows.size()) chunk_rows = host_rows.size();
+        const size_t need = 2 * chunk_rows * row_bytes;
         if (need > x->h_pin_bytes) {
             if (x->h_pin) cudaFreeHost(x->h_pin);
             x->h_pin = nullptr; x->h_pin_bytes = 0;
             CU(cudaMallocHost(&x->h_pin, need));
             x->h_pin_bytes = need;
         }
-        memset(x->h_pin, 0, need);
-        // runs of consecutive slots go up as one copy
-        size_t i = 0;
-        for (size_t r = 0; r < host_rows.size(); r++) memcpy(x->h_pin + r * x->dpad, host_rows[r].second, d * 4ull);
-        while (i < host_rows.size()) {
-            size_t j = i + 1;
-            while (j < host_rows.size() && host_rows[j].first == host_rows[j - 1].first + 1) j++;
-            CU(cudaMemcpyAsync(x->d_vectors + (size_t)host_rows[i].first * x->dpad, x->h_pin + i * x->dpad, (j - i) * (size_t)x->dpad * 4, cudaMemcpyHostToDevice, x->stream));
-            i = j;
+        cudaEvent_t done[2] = {nullptr, nullptr};
+        struct EvGuard { cudaEvent_t *e; ~EvGuard() { for (int i = 0; i < 2; i++) if (e[i]) cudaEventDestroy(e[i]); } } guard{done};
+        CU(cudaEventCreateWithFlags(&done[0], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&done[1], cudaEventDisableTiming));
+        const bool padded = x->dpad != d;
+        int b = 0;
+        for (size_t c0 = 0; c0 < host_rows.size(); c0 += chunk_rows, b ^= 1) {
+            const size_t c1 = std::min(host_rows.size(), c0 + chunk_rows);
+            float *buf = x->h_pin + (size_t)b * chunk_rows * x->dpad;
+            CU(cudaEventSynchronize(done[b])); // the copies that read this buffer two chunks ago (no-op for a fresh event)
+            if (padded) memset(buf, 0, (c1 - c0) * row_bytes);
+            for (size_t r = c0; r < c1; r++) memcpy(buf + (r - c0) * x->dpad, host_rows[r].second, d * 4ull);
+            size_t i = c0;
+            while (i < c1) { // runs of consecutive slots go up as one copy
+                size_t j = i + 1;
+                while (j < c1 && host_rows[j].first == host_rows[j - 1].first + 1) j++;
+                CU(cudaMemcpyAsync(x->d_vectors + (size_t)host_rows[i].first * x->dpad, buf + (i - c0) * x->dpad, (j - i) * row_bytes, cudaMemcpyHostToDevice, x->stream));
+                i = j;
+            }
+            CU(cudaEventRecord(done[b], x->stream));
         }
+        CU(cudaEventSynchronize(done[0]));
+        CU(cudaEventSynchronize(done[1]));
     }
     for (auto &run : dev_runs)
         CU(cudaMemcpy2DAsync(x->d_vectors + (size_t)run.first * x->dpad, x->dpad * 4ull, run.second.first, d * 4ull, d * 4ull, run.second.second, cudaMemcpyDeviceToDevice, x->stream));
