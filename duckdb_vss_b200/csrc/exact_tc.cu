@@ -125,21 +125,27 @@ struct TcParams {
     unsigned long long *part_key; // [split][nq][kCand] (order-key << 32 | row)
     float *part_score;            // [split][nq][kCand]
     float *dbg_dots;              // optional [nq][n] raw q·b (validation of the tensor-core path)
+    uint32_t *shared_worst;       // [nq] order key of the smallest 'worst kept score' any CTA has reached for the query (0xFFFFFFFF = none)
 };
 
-// QRES: the query tile (hi + lo planes of every K block) stays resident in shared memory for the whole CTA and only the
-// base tiles stream through the ring — half the L2->SM traffic per tile. Needs dk <= 128 (128 KB of queries + 3 x 32 KB).
-template <bool QRES>
+// MODE 0: every ring stage carries (Q_hi, Q_lo, B_hi, B_lo) of one K block — 64 KB per stage, any dk.
+// MODE 1 (dk <= 64): the query tile (hi + lo planes of every K block) stays resident in shared memory for the whole CTA and
+//         only (B_hi, B_lo) stream through the ring — half the L2->SM traffic per tile.
+// MODE 2 (dk <= 128): only the hi plane of the query tile is resident (64 KB at dk = 128); a stage carries (Q_lo, B_hi, B_lo) —
+//         three quarters of the streamed bytes of MODE 0, which is what bounds the kernel (L2->SM operand stream).
+template <int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1)
 k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__ CUtensorMap map_q_lo,
            const __grid_constant__ CUtensorMap map_b_hi, const __grid_constant__ CUtensorMap map_b_lo, TcParams p) {
+    constexpr bool QRES = MODE == 1, HIRES = MODE == 2;
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *tiles = reinterpret_cast<unsigned char *>((reinterpret_cast<uintptr_t>(smem) + 1023) & ~uintptr_t(1023));
-    constexpr uint32_t stage_bytes = QRES ? 2 * kTileBytes : kStageBytes;   // ring stage: (B_hi, B_lo) or (Q_hi, Q_lo, B_hi, B_lo)
-    constexpr uint32_t b_off = QRES ? 0u : 2 * kTileBytes;                  // offset of B_hi inside a stage
+    constexpr uint32_t stage_bytes = QRES ? 2 * kTileBytes : (HIRES ? 3 * kTileBytes : kStageBytes);
+    constexpr uint32_t b_off = QRES ? 0u : (HIRES ? kTileBytes : 2 * kTileBytes);   // offset of B_hi inside a stage
     constexpr uint32_t NST = QRES ? kStages : kStagesStream;
-    unsigned char *qres = tiles + NST * stage_bytes;                        // QRES: [kblock][hi, lo] tiles
-    unsigned char *after = qres + (QRES ? (p.dk / kKB) * 2 * kTileBytes : 0u);
+    constexpr uint32_t res_tiles = QRES ? 2u : (HIRES ? 1u : 0u);              // resident query tiles per K block
+    unsigned char *qres = tiles + NST * stage_bytes;                            // resident: [kblock][hi(, lo)] tiles
+    unsigned char *after = qres + (p.dk / kKB) * res_tiles * kTileBytes;
     float *cl_s = reinterpret_cast<float *>(after);                          // [128 queries][kCand] candidate scores, ascending
     uint32_t *cl_r = reinterpret_cast<uint32_t *>(after + kTM * kCand * 4);  // ... and rows
     float *sc = reinterpret_cast<float *>(after + 2 * kTM * kCand * 4);      // [128 queries][36] scores of the current 32-column chunk
@@ -174,11 +180,11 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
-            if (QRES && ntiles) {
-                mbar_arrive_expect(q_full, kblocks * 2 * kTileBytes);
+            if (res_tiles && ntiles) {
+                mbar_arrive_expect(q_full, kblocks * res_tiles * kTileBytes);
                 for (uint32_t kb = 0; kb < kblocks; kb++) {
-                    tma_tile_2d(qres + (kb * 2 + 0) * kTileBytes, &map_q_hi, (int)(kb * kKB), (int)q0, q_full);
-                    tma_tile_2d(qres + (kb * 2 + 1) * kTileBytes, &map_q_lo, (int)(kb * kKB), (int)q0, q_full);
+                    tma_tile_2d(qres + (kb * res_tiles + 0) * kTileBytes, &map_q_hi, (int)(kb * kKB), (int)q0, q_full);
+                    if (QRES) tma_tile_2d(qres + (kb * 2 + 1) * kTileBytes, &map_q_lo, (int)(kb * kKB), (int)q0, q_full);
                 }
             }
             uint32_t it = 0;
@@ -189,9 +195,11 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
                     mbar_wait_relaxed(&empty[s], ph ^ 1u);
                     unsigned char *st = tiles + s * stage_bytes;
                     mbar_arrive_expect(&full[s], stage_bytes);
-                    if (!QRES) {
+                    if (MODE == 0) {
                         tma_tile_2d(st + 0 * kTileBytes, &map_q_hi, (int)(kb * kKB), (int)q0, &full[s]);
                         tma_tile_2d(st + 1 * kTileBytes, &map_q_lo, (int)(kb * kKB), (int)q0, &full[s]);
+                    } else if (HIRES) {
+                        tma_tile_2d(st, &map_q_lo, (int)(kb * kKB), (int)q0, &full[s]);
                     }
                     tma_tile_2d(st + b_off, &map_b_hi, (int)(kb * kKB), row0, &full[s]);
                     tma_tile_2d(st + b_off + kTileBytes, &map_b_lo, (int)(kb * kKB), row0, &full[s]);
@@ -204,7 +212,7 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
             // kind::tf32, D = F32, A/B = TF32, both K-major, N = 128, M = 128
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTN >> 3) << 17) | ((uint32_t)(kTM >> 4) << 24);
             uint32_t it = 0;
-            if (QRES && ntiles) mbar_wait(q_full, 0);
+            if (res_tiles && ntiles) mbar_wait(q_full, 0);
             for (uint32_t t = 0; t < ntiles; t++) {
                 const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
                 mbar_wait_relaxed(&acc_empty[buf], aph ^ 1u);
@@ -215,8 +223,9 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
                     mbar_wait_relaxed(&full[s], ph);
                     tc_fence_after();
                     unsigned char *st = tiles + s * stage_bytes;
-                    const unsigned char *qt = QRES ? qres + kb * 2 * kTileBytes : st;
-                    const uint64_t qh = umma_desc_sw128(qt), ql = umma_desc_sw128(qt + kTileBytes);
+                    const unsigned char *qht = res_tiles ? qres + kb * res_tiles * kTileBytes : st;
+                    const unsigned char *qlt = QRES ? qht + kTileBytes : (HIRES ? st : st + kTileBytes);
+                    const uint64_t qh = umma_desc_sw128(qht), ql = umma_desc_sw128(qlt);
                     const uint64_t bh = umma_desc_sw128(st + b_off), bl = umma_desc_sw128(st + b_off + kTileBytes);
 #pragma unroll
                     for (uint32_t k = 0; k < kKB / 8; k++) { // UMMA_K = 8 for TF32: 32 bytes along K inside the swizzle row
@@ -247,6 +256,17 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
         for (uint32_t t = 0; t < ntiles; t++) {
             const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
             const uint64_t row0 = r_begin + (uint64_t)t * kTN;
+            // The CTAs that scan other row ranges for the same queries publish the worst score of their (full) lists: a row
+            // at or above ANY full list's worst score cannot be among the best kCand of the union, so the tightest published
+            // value is a valid threshold here too — it cuts the list insertions (the critical path of this kernel) by about
+            // the number of splits. A stale value only prunes less.
+            if (qvalid) {
+                const uint32_t wk = __ldcg(p.shared_worst + qi);
+                if (wk != 0xFFFFFFFFu) {
+                    const float wv = __uint_as_float((wk & 0x80000000u) ? (wk & 0x7FFFFFFFu) : ~wk); // inverse of order_key
+                    worst = fminf(worst, wv);
+                }
+            }
             // norms of this tile's 128 base rows: loaded before the wait on the accumulator so that the L2 round trip
             // overlaps it, staged once per warp (zero beyond the end: those columns never pass)
             float bnr[kTN / 32];
@@ -312,7 +332,10 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
                     ls[lane] = e;
                     lr[lane] = r;
                     const float w31 = __shfl_sync(kFull, e, kCand - 1);
-                    if (lane == qq) worst = w31;
+                    if (lane == qq && w31 < worst) {
+                        worst = w31;
+                        atomicMin(p.shared_worst + qi, order_key_f(w31));
+                    }
                 }
                 __syncwarp();
             }
@@ -494,7 +517,7 @@ cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, con
             pool_set[dev] = true;
         }
     }
-    DevBuf b_hi(st), b_lo(st), q_hi(st), q_lo(st), bn2(st), qn2(st), pk(st), ps(st), ck(st), cs(st), fl(st), mx(st);
+    DevBuf b_hi(st), b_lo(st), q_hi(st), q_lo(st), bn2(st), qn2(st), pk(st), ps(st), ck(st), cs(st), fl(st), mx(st), sw(st);
     cudaError_t e;
 #define TRY(x) do { e = (x); if (e != cudaSuccess) return e; } while (0)
     TRY(b_hi.alloc(n * dk * 4)); TRY(b_lo.alloc(n * dk * 4)); TRY(q_hi.alloc(nq * dk * 4)); TRY(q_lo.alloc(nq * dk * 4));
@@ -524,19 +547,31 @@ cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, con
     splits = (n + rows_per_split - 1) / rows_per_split;
     TRY(pk.alloc(splits * nq * kCand * 8)); TRY(ps.alloc(splits * nq * kCand * 4));
     TRY(ck.alloc(nq * kCand * 8)); TRY(cs.alloc(nq * kCand * 4)); TRY(fl.alloc(nq * 4));
+    TRY(sw.alloc(nq * 4));
+    TRY(cudaMemsetAsync(sw.p, 0xFF, nq * 4, st));
     TcParams p{};
     p.n = n; p.nq = nq; p.rows_per_split = rows_per_split; p.dk = dk; p.metric = metric;
     p.bnorm2 = bn2.as<float>(); p.qnorm2 = qn2.as<float>();
     p.part_key = pk.as<unsigned long long>(); p.part_score = ps.as<float>(); p.dbg_dots = dbg_dots;
-    const bool qres = dk <= 64; // query tile resident: 2*dk/32 tiles of 16 KB next to 3 x 32 KB stages and 48 KB of lists
+    p.shared_worst = sw.as<uint32_t>();
+    // operand placement (see k_tiles_tc): dk <= 64 whole query tile resident, dk <= 128 its hi plane, else everything streams
+    static const int forced = [] { const char *e = getenv("GVSS_TC_MODE"); return e ? atoi(e) : -1; }();
+    int mode = dk <= 64 ? 1 : (dk <= 128 ? 2 : 0);
+    if (forced == 0) mode = 0;
     const size_t lists = 2 * (size_t)kTM * kCand * 4 + (size_t)kTM * kScStride * 4 + 4 * (size_t)kTN * 4; // lists + scores + norms
-    const size_t smem = (qres ? (size_t)kStages * 2 * kTileBytes + (size_t)(dk / kKB) * 2 * kTileBytes : (size_t)kStagesStream * kStageBytes) + lists + 1024 + 256;
-    if (qres) {
-        TRY(cudaFuncSetAttribute(k_tiles_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tiles_tc<true><<<dim3((unsigned)qtiles, (unsigned)splits), kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
+    const size_t ring = mode == 1 ? (size_t)kStages * 2 * kTileBytes : (mode == 2 ? (size_t)kStagesStream * 3 * kTileBytes : (size_t)kStagesStream * kStageBytes);
+    const size_t resident = (size_t)(dk / kKB) * (mode == 1 ? 2 : (mode == 2 ? 1 : 0)) * kTileBytes;
+    const size_t smem = ring + resident + lists + 1024 + 256;
+    const dim3 grid((unsigned)qtiles, (unsigned)splits);
+    if (mode == 1) {
+        TRY(cudaFuncSetAttribute(k_tiles_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tiles_tc<1><<<grid, kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
+    } else if (mode == 2) {
+        TRY(cudaFuncSetAttribute(k_tiles_tc<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tiles_tc<2><<<grid, kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
     } else {
-        TRY(cudaFuncSetAttribute(k_tiles_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tiles_tc<false><<<dim3((unsigned)qtiles, (unsigned)splits), kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
+        TRY(cudaFuncSetAttribute(k_tiles_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tiles_tc<0><<<grid, kTcThreads, smem, st>>>(mqh, mql, mbh, mbl, p);
     }
     count_launch();
     TRY(cudaGetLastError());
