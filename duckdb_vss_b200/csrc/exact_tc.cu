@@ -21,6 +21,7 @@
 #include "exact_common.cuh"
 
 #include <cuda.h>
+#include <algorithm>
 #include <cstdio>
 
 namespace gvss {
@@ -482,20 +483,13 @@ static cudaError_t rerank_t(const float *base, uint64_t n, const int64_t *keys, 
     return cudaGetLastError();
 }
 
-__global__ void k_max(const float *x, uint64_t n, float *out) { // single CTA is enough: called once per base set
-    __shared__ float sm[32];
+// maximum of non-negative floats (squared norms): their bit patterns order like unsigned integers; *out starts at 0
+__global__ void k_max(const float *x, uint64_t n, float *out) {
     float m = 0.f;
-    for (uint64_t i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, x[i]);
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) m = fmaxf(m, x[i]);
 #pragma unroll
     for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, o));
-    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        m = threadIdx.x < blockDim.x / 32 ? sm[threadIdx.x] : 0.f;
-#pragma unroll
-        for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, o));
-        if (threadIdx.x == 0) *out = m;
-    }
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<unsigned int *>(out), __float_as_uint(m));
 }
 
 // Returns cudaErrorNotSupported when the shape does not fit this path (caller then uses k_exact alone).
@@ -524,7 +518,8 @@ cudaError_t launch_exact_topk_tc(char metric, const float *base, uint64_t n, con
     TRY(bn2.alloc(n * 4)); TRY(qn2.alloc(nq * 4)); TRY(mx.alloc(4));
     k_split<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(base, n, d, dk, b_hi.as<float>(), b_lo.as<float>(), bn2.as<float>());
     k_split<<<(unsigned)((nq + 7) / 8), 256, 0, st>>>(queries, nq, d, dk, q_hi.as<float>(), q_lo.as<float>(), qn2.as<float>());
-    k_max<<<1, 1024, 0, st>>>(bn2.as<float>(), n, mx.as<float>());
+    cudaMemsetAsync(mx.p, 0, 4, st);
+    k_max<<<(unsigned)std::min<uint64_t>(592, (n + 1023) / 1024), 256, 0, st>>>(bn2.as<float>(), n, mx.as<float>());
     count_launch(3);
     CUtensorMap mqh, mql, mbh, mbl;
     if (!make_map(&mqh, q_hi.as<float>(), nq, dk) || !make_map(&mql, q_lo.as<float>(), nq, dk) || !make_map(&mbh, b_hi.as<float>(), n, dk) ||
