@@ -23,6 +23,7 @@
 #include <cuda.h>
 #include <algorithm>
 #include <cstdio>
+#include <type_traits>
 
 namespace gvss {
 
@@ -30,6 +31,12 @@ constexpr int kTM = 128;     // queries per tile (UMMA M)
 constexpr int kTN = 128;     // base rows per tile (UMMA N)
 constexpr int kKB = 32;      // floats per K block = one 128-byte swizzle row
 constexpr int kStages = 3;        // ring depth of the query-resident variant (32 KB stages)
+#ifndef GVSS_TC_PROF
+#define GVSS_TC_PROF 0 // per-role clocks of one CTA on stdout (tuning aid)
+#endif
+#ifndef GVSS_TC_WAIT_HINT
+#define GVSS_TC_WAIT_HINT 2000
+#endif
 constexpr int kStagesStream = 2;  // ring depth when the query tile streams too (64 KB stages)
 constexpr int kCand = 32;    // candidates kept per query
 constexpr uint32_t kTileBytes = kTM * kKB * 4; // 16 KB per operand tile
@@ -76,7 +83,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity
         "bra WAITR_%=;\n"
         "DONER_%=:\n"
         "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity), "r"(2000u)
+        "r"(parity), "r"((uint32_t)GVSS_TC_WAIT_HINT)
         : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -214,14 +221,29 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTN >> 3) << 17) | ((uint32_t)(kTM >> 4) << 24);
             uint32_t it = 0;
             if (res_tiles && ntiles) mbar_wait(q_full, 0);
+#if GVSS_TC_PROF
+            long long pw_acc = 0, pw_full = 0, p_t0 = clock64();
+#endif
             for (uint32_t t = 0; t < ntiles; t++) {
                 const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
+#if GVSS_TC_PROF
+                const long long a0 = clock64();
+#endif
                 mbar_wait_relaxed(&acc_empty[buf], aph ^ 1u);
+#if GVSS_TC_PROF
+                pw_acc += clock64() - a0;
+#endif
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * kTN;
                 for (uint32_t kb = 0; kb < kblocks; kb++, it++) {
                     const uint32_t s = it % NST, ph = (it / NST) & 1u;
+#if GVSS_TC_PROF
+                    const long long f0 = clock64();
+#endif
                     mbar_wait_relaxed(&full[s], ph);
+#if GVSS_TC_PROF
+                    pw_full += clock64() - f0;
+#endif
                     tc_fence_after();
                     unsigned char *st = tiles + s * stage_bytes;
                     const unsigned char *qht = res_tiles ? qres + kb * res_tiles * kTileBytes : st;
@@ -239,6 +261,9 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
                 }
                 umma_commit(&acc_full[buf]);
             }
+#if GVSS_TC_PROF
+            if (blockIdx.x == 3 && blockIdx.y == 2) printf("MMA thread: tiles %u total %lld wait_acc_empty %lld wait_full %lld (cycles)\n", ntiles, clock64() - p_t0, pw_acc, pw_full);
+#endif
         }
     } else {
         // ===== epilogue: thread <-> query row (TMEM lane) for the scores, warp <-> query for the candidate lists =====
@@ -254,6 +279,9 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
         }
         __syncwarp();
         float worst = CUDART_INF_F; // this thread's query: score of its current worst kept candidate
+#if GVSS_TC_PROF
+        long long ew_acc = 0, e_ld = 0, e_p1 = 0, e_p2 = 0, e_t0 = clock64();
+#endif
         for (uint32_t t = 0; t < ntiles; t++) {
             const uint32_t buf = t & 1u, aph = (t >> 1) & 1u;
             const uint64_t row0 = r_begin + (uint64_t)t * kTN;
@@ -273,7 +301,13 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
             float bnr[kTN / 32];
 #pragma unroll
             for (int c = 0; c < kTN / 32; c++) bnr[c] = row0 + c * 32 + lane < r_end ? __ldg(&p.bnorm2[row0 + c * 32 + lane]) : 0.f;
+#if GVSS_TC_PROF
+            const long long w0 = clock64();
+#endif
             mbar_wait_relaxed(&acc_full[buf], aph);
+#if GVSS_TC_PROF
+            ew_acc += clock64() - w0;
+#endif
             tc_fence_after();
             float *bnw = bn_s + quarter * kTN;
 #pragma unroll
@@ -282,7 +316,14 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
             const uint32_t valid_cols = (uint32_t)min((uint64_t)kTN, r_end - row0);
             for (uint32_t c0 = 0; c0 < kTN; c0 += 32) {
                 float acc[32];
+#if GVSS_TC_PROF
+                const long long l0 = clock64();
+#endif
                 tmem_ld32(tmem_base + ((quarter * 32u) << 16) + buf * kTN + c0, acc);
+#if GVSS_TC_PROF
+                const long long l1 = clock64();
+                e_ld += l1 - l0;
+#endif
                 if (p.dbg_dots && qvalid) {
 #pragma unroll
                     for (int j = 0; j < 32; j++) if (c0 + j < valid_cols) p.dbg_dots[qi * p.n + row0 + c0 + j] = acc[j];
@@ -290,24 +331,39 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
                 // phase 1 (straight-line, thread <-> query): scores of 32 columns into shared memory, bit mask of the
                 // columns that beat this query's threshold
                 uint32_t pass = 0;
+                auto phase1 = [&](auto metric_tag) { // metric fixed at compile time inside the straight-line block
+                    constexpr int MT = decltype(metric_tag)::value;
+                    uint32_t pmask[8];
 #pragma unroll
-                for (int j4 = 0; j4 < 8; j4++) {
-                    const float4 bn = *reinterpret_cast<const float4 *>(bnw + c0 + j4 * 4);
-                    const float b4[4] = {bn.x, bn.y, bn.z, bn.w};
-                    float s4[4];
+                    for (int j4 = 0; j4 < 8; j4++) {
+                        const float4 bn = *reinterpret_cast<const float4 *>(bnw + c0 + j4 * 4);
+                        const float b4[4] = {bn.x, bn.y, bn.z, bn.w};
+                        float s4[4];
+                        uint32_t m4 = 0; // independent per group of four: no 32-long dependent chain on `pass`
 #pragma unroll
-                    for (int e = 0; e < 4; e++) {
-                        const float a = acc[j4 * 4 + e];
-                        if (p.metric == 'e') s4[e] = fmaf(-2.f, a, b4[e]);
-                        else if (p.metric == 'i') s4[e] = -a;
-                        else s4[e] = -a * rsqrtf(fmaxf(qn2 * b4[e], 1e-30f));
-                        pass |= (s4[e] < worst) ? (1u << (j4 * 4 + e)) : 0u;
+                        for (int e = 0; e < 4; e++) {
+                            const float a = acc[j4 * 4 + e];
+                            if (MT == 'e') s4[e] = fmaf(-2.f, a, b4[e]);
+                            else if (MT == 'i') s4[e] = -a;
+                            else s4[e] = -a * rsqrtf(fmaxf(qn2 * b4[e], 1e-30f));
+                            m4 |= (s4[e] < worst) ? (1u << e) : 0u;
+                        }
+                        pmask[j4] = m4;
+                        *reinterpret_cast<float4 *>(sc + qrow * kScStride + j4 * 4) = make_float4(s4[0], s4[1], s4[2], s4[3]);
                     }
-                    *reinterpret_cast<float4 *>(sc + qrow * kScStride + j4 * 4) = make_float4(s4[0], s4[1], s4[2], s4[3]);
-                }
+                    pass = (pmask[0] | (pmask[1] << 4)) | ((pmask[2] << 8) | (pmask[3] << 12)) |
+                           (((pmask[4] << 16) | (pmask[5] << 20)) | ((pmask[6] << 24) | (pmask[7] << 28)));
+                };
+                if (p.metric == 'e') phase1(std::integral_constant<int, 'e'>{});
+                else if (p.metric == 'i') phase1(std::integral_constant<int, 'i'>{});
+                else phase1(std::integral_constant<int, 'c'>{});
                 const uint32_t colmask = valid_cols >= c0 + 32 ? 0xFFFFFFFFu : (valid_cols > c0 ? (1u << (valid_cols - c0)) - 1u : 0u);
                 pass = qvalid ? (pass & colmask) : 0u;
                 __syncwarp();
+#if GVSS_TC_PROF
+                const long long l2 = clock64();
+                e_p1 += l2 - l1;
+#endif
                 // phase 2 (warp <-> query): sorted insertion with one ballot and one shuffle per candidate; equal scores
                 // keep the earlier row first
                 uint32_t qmask = __ballot_sync(kFull, pass != 0u);
@@ -339,10 +395,17 @@ k_tiles_tc(const __grid_constant__ CUtensorMap map_q_hi, const __grid_constant__
                     }
                 }
                 __syncwarp();
+#if GVSS_TC_PROF
+                e_p2 += clock64() - l2;
+#endif
             }
             tc_fence_before();
             mbar_arrive(&acc_empty[buf]);
         }
+#if GVSS_TC_PROF
+        if (blockIdx.x == 3 && blockIdx.y == 2 && warp == 2 && lane == 0)
+            printf("epilogue warp 2: total %lld wait_acc_full %lld tmem_ld %lld phase1 %lld phase2 %lld (cycles)\n", clock64() - e_t0, ew_acc, e_ld, e_p1, e_p2);
+#endif
         for (uint32_t qq = 0; qq < 32; qq++) { // lists out: warp-wide, one entry per lane
             const uint64_t q = q0 + quarter * 32 + qq;
             if (q >= p.nq) break;
