@@ -194,7 +194,10 @@ uint32_t resident_warps(int device, uint32_t smem_bytes, bool build) {
     uint32_t by_smem = (uint32_t)(smem_per_sm[device] / (smem_bytes + 1024)); // 1 KB is reserved per CTA
     // 32 = CTA-per-SM limit; build warps also hold a node lock at times; k_search is compiled for 80 registers
     // (__launch_bounds__(32, GVSS_SEARCH_MIN_BLOCKS)): 65536 / (80 * 32) = 25 warps fit the register file
-    const uint32_t cap = build ? 16u : 25u;
+#ifndef GVSS_SEARCH_WARPS_CAP
+#define GVSS_SEARCH_WARPS_CAP 25
+#endif
+    const uint32_t cap = build ? 16u : (uint32_t)GVSS_SEARCH_WARPS_CAP;
     if (by_smem > cap) by_smem = cap;
     if (by_smem < 1) by_smem = 1;
     return by_smem * (uint32_t)sm_count[device];
