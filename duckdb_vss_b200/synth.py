@@ -54,6 +54,10 @@ def config(name, n=None, nq=None):
         for a in (base, q):
             a /= np.linalg.norm(a, axis=1, keepdims=True)
         return {"metric": "ip", "base": base, "queries": q, "k": 10}
+    if name == "join10m":  # config 5: 100k queries x 10M x 128 l2sq, generator as sift1m at 10M (C = N/100), seed 48
+        n = n or 10_000_000
+        base, q = clustered(n, 128, max(1024, n // 100), 16, 48, nq or 100_000)
+        return {"metric": "l2sq", "base": base, "queries": q, "k": 10}
     raise KeyError(name)
 
 

@@ -23,9 +23,9 @@ EF_SWEEP = (32, 64, 128, 256, 384, 512)
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["text768", "deep10m", "sift1m"])
+    ap.add_argument("config", choices=["text768", "deep10m", "sift1m", "join10m"])
     ap.add_argument("--vectors", type=int, default=0)
-    ap.add_argument("--nq", type=int, default=10_000)
+    ap.add_argument("--nq", type=int, default=0, help="0 = the config's own query count")
     ap.add_argument("--check-queries", type=int, default=300, help="queries replayed on the compiled reference (0 = skip)")
     ap.add_argument("--steps", type=int, default=3)
     args = ap.parse_args()
@@ -35,7 +35,7 @@ def main():
     from duckdb_vss_b200 import synth, index as gvi
 
     t0 = time.perf_counter()
-    cfg = synth.config(args.config, n=args.vectors or None, nq=args.nq)
+    cfg = synth.config(args.config, n=args.vectors or None, nq=args.nq or None)
     base_np, q_np, metric, k = cfg["base"], cfg["queries"], cfg["metric"], cfg["k"]
     n, d = base_np.shape
     nq = q_np.shape[0]
