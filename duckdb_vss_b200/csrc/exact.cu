@@ -261,11 +261,94 @@ __global__ void k_merge(const unsigned long long *__restrict__ in_key, const flo
     }
 }
 
+// Merge of `shards` lists that are each ASCENDING in their 64-bit sort key (MODE 0 partials: order key << 32 | row, padding
+// ~0 at the end), k <= 32 entries per list: a tree of pairwise merges cut at k, lane i holding entry i of both lists and
+// ranking it in the other list by binary search (5 steps) — about twenty times fewer comparisons than the rank sort over
+// shards * k entries. A query with a list that is not ascending (NaN scores are inserted in front by the tensor-core
+// kernel) is ranked by the generic rule instead; results are identical either way.
+__global__ void k_merge_sorted(const unsigned long long *__restrict__ in_key, const float *__restrict__ in_dist, uint32_t shards,
+                               uint64_t nq, uint32_t k, const int64_t *__restrict__ id_map, int64_t *__restrict__ keys_out,
+                               float *__restrict__ dist_out) {
+    extern __shared__ __align__(16) unsigned long long merge_smem[];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint64_t q = (uint64_t)blockIdx.x * (blockDim.x / 32) + warp;
+    if (q >= nq) return;
+    const uint32_t half = (shards + 1) / 2;
+    // per warp: keys A [shards][32], keys B [half][32], origins A, origins B (entry index inside the input)
+    unsigned long long *base = merge_smem + (size_t)warp * ((size_t)(shards + half) * 32 + (size_t)(shards + half) * 16);
+    unsigned long long *kA = base, *kB = base + (size_t)shards * 32;
+    uint32_t *oA = reinterpret_cast<uint32_t *>(kB + (size_t)half * 32), *oB = oA + (size_t)shards * 32;
+    bool sorted = true;
+    for (uint32_t l = 0; l < shards; l++) {
+        const unsigned long long key = lane < k ? in_key[((size_t)l * nq + q) * k + lane] : ~0ull;
+        kA[l * 32 + lane] = key;
+        oA[l * 32 + lane] = l * k + lane;
+        const unsigned long long nxt = __shfl_down_sync(0xFFFFFFFFu, key, 1);
+        sorted &= lane == 31 || key <= nxt;
+    }
+    __syncwarp();
+    if (__ballot_sync(0xFFFFFFFFu, !sorted)) { // generic rank sort over all entries (rare)
+        const uint32_t total = shards * 32;
+        for (uint32_t e = lane; e < total; e += 32) {
+            const unsigned long long key = kA[e];
+            uint32_t rank = 0;
+            for (uint32_t o = 0; o < total; o++) { const unsigned long long x = kA[o]; rank += (x < key || (x == key && o < e)) ? 1u : 0u; }
+            if (rank < k) {
+                const uint32_t org = oA[e];
+                int64_t id = -1;
+                if (key != ~0ull) { const uint32_t row = (uint32_t)(key & 0xFFFFFFFFull); id = id_map ? id_map[row] : (int64_t)row; }
+                keys_out[q * k + rank] = id;
+                if (dist_out) dist_out[q * k + rank] = key != ~0ull ? in_dist[((size_t)(org / k) * nq + q) * k + org % k] : CUDART_INF_F;
+            }
+        }
+        return;
+    }
+    uint32_t n = shards;
+    while (n > 1) {
+        const uint32_t pairs = n / 2;
+        for (uint32_t p = 0; p < pairs; p++) {
+            const unsigned long long *X = kA + (2 * p) * 32, *Y = kA + (2 * p + 1) * 32;
+            const unsigned long long x = X[lane], y = Y[lane];
+            uint32_t lo = 0, hi = 32; // #{Y < x}
+            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (Y[mid] < x) lo = mid + 1; else hi = mid; }
+            const uint32_t rx = lane + lo;
+            lo = 0; hi = 32;          // #{X <= y}
+            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (X[mid] <= y) lo = mid + 1; else hi = mid; }
+            const uint32_t ry = lane + lo;
+            if (rx < 32) { kB[p * 32 + rx] = x; oB[p * 32 + rx] = oA[(2 * p) * 32 + lane]; }
+            if (ry < 32) { kB[p * 32 + ry] = y; oB[p * 32 + ry] = oA[(2 * p + 1) * 32 + lane]; }
+        }
+        if (n & 1u) { kB[pairs * 32 + lane] = kA[(n - 1) * 32 + lane]; oB[pairs * 32 + lane] = oA[(n - 1) * 32 + lane]; }
+        __syncwarp();
+        n = (n + 1) / 2;
+        for (uint32_t l = 0; l < n; l++) { kA[l * 32 + lane] = kB[l * 32 + lane]; oA[l * 32 + lane] = oB[l * 32 + lane]; }
+        __syncwarp();
+    }
+    if (lane < k) {
+        const unsigned long long key = kA[lane];
+        const uint32_t org = oA[lane];
+        int64_t id = -1;
+        if (key != ~0ull) { const uint32_t row = (uint32_t)(key & 0xFFFFFFFFull); id = id_map ? id_map[row] : (int64_t)row; }
+        keys_out[q * k + lane] = id;
+        if (dist_out) dist_out[q * k + lane] = key != ~0ull ? in_dist[((size_t)(org / k) * nq + q) * k + org % k] : CUDART_INF_F;
+    }
+}
+
 template <int MODE>
 static cudaError_t launch_merge(const unsigned long long *in_key, const float *in_dist, uint32_t shards, uint64_t nq, uint32_t k,
                                 const int64_t *id_map, int64_t *keys_out, float *dist_out, cudaStream_t st) {
     const uint32_t wpb = 4, total = shards * k;
     const unsigned grid = (unsigned)((nq + wpb - 1) / wpb);
+    if (MODE == 0 && k <= 32 && shards >= 2 && shards <= 64) { // partial lists of k_exact / k_tiles_tc: ascending
+        const uint32_t half = (shards + 1) / 2;
+        const size_t per_warp = ((size_t)(shards + half) * 32 + (size_t)(shards + half) * 16) * 8;
+        if (per_warp * wpb <= 96 * 1024) {
+            if (per_warp * wpb > 48 * 1024) cudaFuncSetAttribute(k_merge_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            k_merge_sorted<<<grid, wpb * 32, per_warp * wpb, st>>>(in_key, in_dist, shards, nq, k, id_map, keys_out, dist_out);
+            count_launch();
+            return cudaGetLastError();
+        }
+    }
     const size_t smem = (size_t)wpb * total * 16;
     if (total <= 32 * kMergePerLane && smem <= 48 * 1024) k_merge<MODE, true><<<grid, wpb * 32, smem, st>>>(in_key, in_dist, shards, nq, k, id_map, keys_out, dist_out);
     else k_merge<MODE, false><<<grid, wpb * 32, 0, st>>>(in_key, in_dist, shards, nq, k, id_map, keys_out, dist_out);
