@@ -67,10 +67,10 @@ struct Cand {
 #if GVSS_OPCOUNT
 enum { kOpQueries, kOpHops, kOpNew, kOpHopsLe16, kOpHopsNone, kOpPushes, kOpPrunes, kOpPruneKept, kOpInsBatches, kOpInserted,
        kOpShifted, kOpVisRounds, kOpMaybeBatches, kOpPushLevels, kOpPopLevels, kOpClkSelect, kOpClkGather, kOpClkDist, kOpClkMerge,
-       kOpClkStage, kOpClkWait, kOpClkMath, kOpSteps, kOpClkTotal, kOpClkAccept, kOpClkShift, kOpClkAdj, kOpClkVis, kOpClkShiftLoop, kOpCount };
+       kOpClkStage, kOpClkWait, kOpClkMath, kOpSteps, kOpClkTotal, kOpClkAccept, kOpClkShift, kOpClkAdj, kOpClkVis, kOpClkShiftLoop, kOpPredHit, kOpCount };
 static __device__ unsigned long long g_opcount[kOpCount];
 // per-warp, flushed once per query by k_search; GVSS_OPCOUNT=2 keeps only the phase clocks (less distortion)
-#define OPC(i, v) do { if (GVSS_OPCOUNT == 1 || (i) >= kOpClkSelect || (i) == kOpQueries) w.opc[i] += (unsigned long long)(v); } while (0)
+#define OPC(i, v) do { if (GVSS_OPCOUNT == 1 || ((i) >= kOpClkSelect && (i) != kOpPredHit) || (i) == kOpQueries) w.opc[i] += (unsigned long long)(v); } while (0)
 #define OPCLK(var) const long long var = clock64()
 #else
 #define OPC(i, v) do { } while (0)
@@ -779,6 +779,9 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
     uint32_t scan_from = 0; // LQ: every list entry before this index is expanded
+#if GVSS_OPCOUNT
+    uint32_t pred_slot = kInvalid; // the candidate the previous expansion predicted as next
+#endif
     float ghost = CUDART_INF_F; // LQ: smallest distance among the live entries that fell off the list (still in the reference's queue)
     // LQ: log of the reference's queue operations, written downwards from the end of the overflow area ({d, slot} = push,
     // slot == kInvalid = pop); it may use half of the area, the replayed heap then fits below it
@@ -882,6 +885,10 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         cnt.cycles++;
         cnt.base++;
         OPC(kOpHops, 1);
+#if GVSS_OPCOUNT
+        if (c.s == pred_slot) OPC(kOpPredHit, 1);
+        pred_slot = next_slot;
+#endif
         if ((cnt.flags & 0x80000000u) && lane == 0)
             printf("pop %u slot %u d %.9g radius %.9g heap %u top %u computed %u\n", cnt.base, c.s, c.d, radius, heap_size, top_size, cnt.computed);
         if (INSERT && c.s == new_slot) continue;

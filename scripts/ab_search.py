@@ -71,7 +71,7 @@ def child(args):
     n = fn(buf, 32)
     names = ["queries", "hops", "new", "hops_le16", "hops_none", "pushes", "prunes", "prune_kept", "ins_batches", "inserted",
              "shifted", "vis_rounds", "maybe_batches", "push_levels", "pop_levels", "clk_select", "clk_gather", "clk_dist",
-             "clk_lb", "clk_stage", "clk_wait", "clk_math", "steps", "clk_total", "clk_accept", "clk_shift", "clk_adj", "clk_vis", "clk_shiftloop"]
+             "clk_lb", "clk_stage", "clk_wait", "clk_math", "steps", "clk_total", "clk_accept", "clk_shift", "clk_adj", "clk_vis", "clk_shiftloop", "pred_hit"]
     nqr = max(1, buf[0])
     print("   per query: " + "  ".join(f"{names[i]} {buf[i] / nqr:.1f}" for i in range(1, min(n, len(names)))), flush=True)
 
