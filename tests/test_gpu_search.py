@@ -249,3 +249,33 @@ def test_duplicate_vectors_and_removed_entry_point(checker):
     keys, dist, _ = ix.ef_search(q, 10, 64)
     np.testing.assert_array_equal(keys, want["keys"])
     assert not (keys == entry).any()
+
+
+def test_searches_issued_on_different_streams_do_not_share_scratch_at_the_same_time():
+    """gvss_search_device is asynchronous: two batches issued back to back on two streams use the same visited tables and
+    work counter, so the library orders them on the device (event wait). Results must equal the one-at-a-time results."""
+    import torch
+    n, d, nq, k, ef = 30000, 64, 3000, 10, 96
+    base, q = synth.clustered(n, d, 300, 8, 321, 2 * nq)
+    ix = gv.Index(d, "l2sq", M=16)
+    ix.reserve(n, 1)
+    ix.add_batch(base)
+    ix.flush()
+    dev = torch.device("cuda", 0)
+    qa, qb = torch.from_numpy(q[:nq]).to(dev), torch.from_numpy(q[nq:]).to(dev)
+    outs = [torch.empty((nq, k), dtype=torch.int64, device=dev) for _ in range(4)]
+    dists = [torch.empty((nq, k), dtype=torch.float32, device=dev) for _ in range(4)]
+    cnts = [torch.empty(nq, dtype=torch.int32, device=dev) for _ in range(4)]
+    torch.cuda.synchronize()
+    # one at a time
+    for i, qq in enumerate((qa, qb)):
+        ix.search_device(qq.data_ptr(), nq, k, ef, outs[i].data_ptr(), dists[i].data_ptr(), cnts[i].data_ptr(), 0, 0)
+        torch.cuda.synchronize()
+    # back to back on two streams, several rounds
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    for _ in range(5):
+        ix.search_device(qa.data_ptr(), nq, k, ef, outs[2].data_ptr(), dists[2].data_ptr(), cnts[2].data_ptr(), 0, s1.cuda_stream)
+        ix.search_device(qb.data_ptr(), nq, k, ef, outs[3].data_ptr(), dists[3].data_ptr(), cnts[3].data_ptr(), 0, s2.cuda_stream)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[3])
+    assert torch.equal(dists[0], dists[2]) and torch.equal(dists[1], dists[3])
