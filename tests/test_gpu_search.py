@@ -279,3 +279,30 @@ def test_searches_issued_on_different_streams_do_not_share_scratch_at_the_same_t
     torch.cuda.synchronize()
     assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[3])
     assert torch.equal(dists[0], dists[2]) and torch.equal(dists[1], dists[3])
+
+
+def test_concurrent_host_threads_searching_one_index():
+    """InitializeScan runs under the extension's SHARED lock (hnsw_index.cpp:301-303): several host threads may call
+    gvss_search on one index at the same time. The library serialises them; every thread gets the single-thread answer."""
+    import threading
+    n, d = 20000, 48
+    base, q = synth.clustered(n, d, 200, 8, 77, 800)
+    ix = gv.Index(d, "cosine", M=16)
+    ix.reserve(n, 1)
+    ix.add_batch(base)
+    ix.flush()
+    want = [ix.ef_search(q[i * 100:(i + 1) * 100], 10, 64)[0] for i in range(8)]
+    got, errs = [None] * 8, []
+
+    def work(i):
+        try:
+            for _ in range(3):
+                got[i] = ix.ef_search(q[i * 100:(i + 1) * 100], 10, 64)[0]
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(8)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs
+    for i in range(8):
+        np.testing.assert_array_equal(got[i], want[i])
