@@ -53,6 +53,7 @@ SIGNATURES = {
     "gvss_flush": (C.c_int, [C.c_void_p]),
     "gvss_remove": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_uint64)]),
     "gvss_compact": (C.c_int, [C.c_void_p]),
+    "gvss_compact_rebuild": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "gvss_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p]),
     "gvss_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p,

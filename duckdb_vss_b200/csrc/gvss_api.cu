@@ -336,10 +336,15 @@ void gvss_destroy(gvss_index *x) {
     delete x;
 }
 
+static void reset_locked(gvss_index *x);
 int gvss_reset(gvss_index *x) {
     if (!x) return fail("null index");
     std::lock_guard<std::mutex> lk(x->mu);
     cudaSetDevice(x->device);
+    reset_locked(x);
+    return 0;
+}
+static void reset_locked(gvss_index *x) {
     free_device(x);
     x->h_keys.clear(); x->h_levels.clear(); x->h_upper_off.clear();
     x->entry = 0; x->max_level = -1; x->n_deleted = 0; x->lookup_valid = false; x->key_to_slot.clear(); x->free_slots.clear();
@@ -348,6 +353,53 @@ int gvss_reset(gvss_index *x) {
     for (auto &v : x->st_keys) v.clear();
     x->st_device.clear(); x->st_device_rows.clear();
     x->staged = 0; x->level_rng = 1;
+}
+
+// rows of the live members, densely packed (row stride = dims), for gvss_compact_rebuild
+__global__ void k_pack_rows(const float *__restrict__ vectors, uint32_t dpad, uint32_t dims, const uint32_t *__restrict__ slots, uint64_t m,
+                            float *__restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m * dims) return;
+    const uint64_t r = i / dims;
+    out[i] = vectors[(size_t)slots[r] * dpad + (uint32_t)(i - r * dims)];
+}
+
+int gvss_compact_rebuild(gvss_index *x, uint64_t *dropped) {
+    if (!x) return fail("null index");
+    std::lock_guard<std::mutex> lk(x->mu);
+    cudaSetDevice(x->device);
+    if (flush_locked(x)) return 1;
+    if (dropped) *dropped = x->n_deleted;
+    if (!x->n_deleted) return 0; // nothing to drop: the graph stays as it is
+    std::vector<uint32_t> live;
+    std::vector<int64_t> keys;
+    live.reserve(x->count); keys.reserve(x->count);
+    for (uint64_t s = 0; s < x->count; s++)
+        if (x->h_keys[s] != INT64_MAX) { live.push_back((uint32_t)s); keys.push_back(x->h_keys[s]); }
+    const uint64_t m = live.size(), cap = x->capacity;
+    const uint32_t d = x->cfg.dimensions;
+    TempDev rows_mem, slots_mem;
+    float *d_rows = nullptr;
+    uint32_t *d_live = nullptr;
+    if (m) {
+        CU(rows_mem.alloc(d_rows, m * d));
+        CU(slots_mem.alloc(d_live, m));
+        CU(cudaMemcpyAsync(d_live, live.data(), m * 4, cudaMemcpyHostToDevice, x->stream));
+        k_pack_rows<<<(unsigned)((m * d + 255) / 256), 256, 0, x->stream>>>(x->d_vectors, x->dpad, d, d_live, m, d_rows);
+        count_launch();
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(x->stream));
+    }
+    const uint32_t threads = x->host_threads;
+    reset_locked(x);                       // frees the old graph (removed members included)
+    if (ensure_capacity(x, cap)) return 1; // same capacity as before
+    x->host_threads = threads;
+    if (m) {
+        x->st_device.emplace_back(d_rows, std::move(keys));
+        x->st_device_rows.push_back(m);
+        x->staged += m;
+        if (flush_locked(x)) return 1;     // bulk build of the live members only
+    }
     return 0;
 }
 

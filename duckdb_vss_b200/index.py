@@ -63,6 +63,12 @@ class Index:
     def compact(self):
         capi.check(capi.lib().gvss_compact(self._h))
 
+    def compact_rebuild(self):
+        """Deleting compaction: rebuilds the graph over the live members; returns how many removed members were dropped."""
+        n = C.c_uint64(0)
+        capi.check(capi.lib().gvss_compact_rebuild(self._h, C.byref(n)))
+        return n.value
+
     def reset(self):
         capi.check(capi.lib().gvss_reset(self._h))
 

@@ -106,6 +106,12 @@ int gvss_set_build_concurrency(gvss_index *index, uint32_t max_concurrent_insert
 int gvss_remove(gvss_index *index, int64_t key, uint64_t *removed);
 /* index.compact(), hnsw_index.cpp:458 */
 int gvss_compact(gvss_index *index);
+/* Deleting compaction (the extension's README.md:69 says PRAGMA hnsw_compact_index prunes deleted
+ * items; index_gt::compact in this usearch version, index.hpp:3007-3096, only re-orders and keeps them): builds a fresh graph
+ * over the live members on the GPU and drops the removed ones, so searches stop traversing tombstones. Capacity and
+ * configuration stay; slot numbers and the graph change, keys do not. *dropped (optional) = members removed. Not called
+ * by gvss_compact: a maintainer opts in by calling it from HNSWIndex::Compact instead. */
+int gvss_compact_rebuild(gvss_index *index, uint64_t *dropped);
 
 /* --- search -------------------------------------------------------------------------------------------------- */
 /* index.ef_search(query, k, ef) for nq queries at once (hnsw_index.cpp:303-309 single query, :359-364 index join).

@@ -141,3 +141,36 @@ def test_sequential_build_counters_equal_the_reference(checker):
     evaluated = st["query_distances"] + st["pair_distances"]
     assert want["computed_distances"] <= evaluated <= 1.06 * want["computed_distances"]
     assert st["rows_written"] >= n - 1
+
+
+def test_compact_rebuild_drops_removed_members():
+    """gvss_compact_rebuild: after removing a third of the members the graph is rebuilt over the rest —
+    same keys, none of the removed ones, capacity kept, nothing left to traverse as a tombstone, recall as a fresh build."""
+    n, d = 12000, 32
+    base, q = synth.clustered(n, d, 120, 6, 31, 300)
+    ix = gv.Index(d, "l2sq", M=16)
+    ix.reserve(n, 1)
+    ix.add_batch(base)
+    ix.flush()
+    assert ix.compact_rebuild() == 0                      # nothing removed: a no-op
+    gone = np.arange(0, n, 3)
+    for key in gone:
+        assert ix.remove(int(key)) == 1
+    cap = ix.capacity()
+    assert ix.compact_rebuild() == len(gone)
+    info = ix.info()
+    assert info["size"] == n - len(gone) and info["node_count"] == n - len(gone) and info["capacity"] == cap
+    keep = np.setdiff1d(np.arange(n), gone)
+    truth, _ = gv.exact_topk("l2sq", base[keep], q, 10, keys=keep.astype(np.int64))
+    keys, dist, counts, st = ix.ef_search(q, 10, 128, stats=True)
+    assert not np.isin(keys, gone).any()
+    assert synth.recall_at_k(keys, truth) > 0.9
+    assert (st["flags"] & 3 == 0).all()
+    # the compacted index persists and reloads like any other
+    iy = gv.Index(d, "l2sq", M=16)
+    iy.load(ix.save())
+    np.testing.assert_array_equal(iy.ef_search(q, 10, 128)[0], keys)
+    # and keeps accepting rows in the freed capacity
+    ix.add_batch(base[gone[:100]], keys=gone[:100].astype(np.int64))
+    ix.flush()
+    assert ix.size() == n - len(gone) + 100
