@@ -211,6 +211,12 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         if (!handle_ || gvss_compact(handle_)) r.error.message = last_error();
         return r;
     }
+    // deleting variant (not in usearch): rebuilds the graph over the live members and drops the removed ones
+    compaction_result_t compact_rebuild() {
+        compaction_result_t r;
+        if (!handle_ || gvss_compact_rebuild(handle_, nullptr)) r.error.message = last_error();
+        return r;
+    }
     void reset() { if (handle_) gvss_reset(handle_); }
 
     gvss_info info_() const {
