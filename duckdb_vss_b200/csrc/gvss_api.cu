@@ -185,7 +185,8 @@ static bool list_queue();
 static uint32_t search_heap_smem(const gvss_index *x, uint32_t limit) {
     static int v = [] { const char *e = getenv("GVSS_HEAP_SMEM"); return e ? atoi(e) : -1; }();
     if (v >= 0) return (uint32_t)v / 32u * 32u;
-    return (list_queue() && !x->n_deleted) ? 32u : default_heap_smem(limit); // 32 entries = the 5 top levels, fits the slack
+    (void)x;
+    return list_queue() ? 32u : default_heap_smem(limit); // 32 entries = the 5 top levels, fits the slack
 }
 // rows of the staging buffer on the search path: 16 halves the shared memory per query (more resident warps); 32 serves
 // a whole 32-neighbour batch in one go. GVSS_STAGE_ROWS overrides for experiments.

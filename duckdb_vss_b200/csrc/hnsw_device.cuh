@@ -767,7 +767,8 @@ __device__ __forceinline__ uint32_t top_upper_bound(const float *td, uint32_t n,
 // an entry that fell off the list equals it — the pop order depends on the history of usearch's heap: the log is
 // replayed on the real heap (cheap: no distance is recomputed) and the search continues with the heap as the queue
 // (flag bit2). If the log ran out of room the search ends with flag bit3 and the caller repeats it with lq = false.
-// Not used when the index holds removed members (they enter the queue but not the list).
+// Removed members (they enter the reference's queue but not its list) wait in a small min-heap of their own and are
+// expanded when they are closer than every live candidate; a tie with a live candidate switches to the real heap as above.
 constexpr uint32_t kExpanded = 0x80000000u;
 constexpr uint32_t kSlotMask = 0x7FFFFFFFu;
 
@@ -824,6 +825,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         if (lane == 0) { w.top_d[0] = radius; w.top_s[0] = start; }
         top_size = 1;
     } else {
+        // a removed entry point is queued but not listed; in list-as-queue mode such members wait in their own min-heap
+        if (lq) heap_push(w, heap_size, radius, start);
         radius = CUDART_INF_F; // reference reads top.top() of an empty buffer here (UB); +inf is the documented choice
     }
     __syncwarp();
@@ -847,24 +850,45 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     break;
                 }
             }
-            bool tie;
+            // removed members (search only): the reference keeps them in its queue but not in the list. Here they wait in a
+            // min-heap of their own (the heap_* storage) and are expanded when they are closer than every live candidate.
+            const bool have_t = heap_size != 0;
+            const Cand tm = have_t ? heap_get(w, 0) : Cand{CUDART_INF_F, kInvalid};
+            bool tie, take_t = false;
             if (cur >= top_size) {
-                // nothing left to expand: the reference's queue is empty or its head fell off the list earlier, i.e. lies
-                // above the radius and ends the search — unless it EQUALS the radius, then the reference expands it
-                tie = top_size == limit && ghost == radius;
-                if (!tie) break;
+                if (have_t && !(tm.d > radius)) { take_t = true; tie = tm.d == ghost; }
+                else {
+                    // nothing left to expand: the reference's queue is empty or its head lies above the radius and ends the
+                    // search — unless an entry that fell off the list EQUALS the radius, then the reference expands it
+                    tie = top_size == limit && ghost == radius;
+                    if (!tie) break;
+                }
             } else {
                 c.d = w.top_d[cur];
                 c.s = w.top_s[cur] & kSlotMask;
-                // an entry outside the list, or a second live candidate, at the same distance as the queue head: the
-                // reference's pop order depends on its heap's history (`later`: conservative, the equal entry may be expanded)
-                tie = c.d == ghost || (nxt < top_size && w.top_d[nxt] == c.d);
-                if (!tie && nxt < top_size && !later) next_slot = w.top_s[nxt] & kSlotMask;
+                if (have_t && tm.d < c.d) { take_t = true; tie = false; }
+                else {
+                    // an entry outside the list, or a second candidate, at the same distance as the queue head: the
+                    // reference's pop order depends on its heap's history (`later`: conservative, the equal entry may be expanded)
+                    tie = c.d == ghost || (nxt < top_size && w.top_d[nxt] == c.d) || (have_t && tm.d == c.d);
+                    if (!tie && nxt < top_size && !later) next_slot = w.top_s[nxt] & kSlotMask;
+                }
+            }
+            if (take_t && !tie) { // two removed members at the same distance: ambiguous as well
+                tie = (heap_size > 1 && heap_get(w, 1).d == tm.d) || (heap_size > 2 && heap_get(w, 2).d == tm.d);
             }
             if (tie) {
                 if (!to_heap()) return;
                 continue; // the same iteration again, with the heap as the queue
             }
+            if (take_t) {
+                c = tm;
+                heap_pop(w, heap_size);
+                if (lane == 0 && logn < log_cap) log_put(logn, 0.0f, kInvalid);
+                log_ok = log_ok && logn < log_cap;
+                logn++;
+                __syncwarp();
+            } else {
             __syncwarp();
             if (lane == 0) {
                 w.top_s[cur] = c.s | kExpanded;
@@ -874,6 +898,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             logn++;
             __syncwarp();
             scan_from = cur + 1;
+            }
         } else {
             if (!heap_size) break;
             c = heap_get(w, 0);
@@ -1015,11 +1040,15 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                     if (w.heap_smem >= 256u && heap_size == w.heap_smem && top_size == limit) heap_prune(w, heap_size, radius);
                     if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
                 }
-            } else { // log the pushes in list order
+            } else { // log the pushes in list order; removed members go to their own heap
                 const uint32_t at = logn + __popc(accmask & lt_mask);
                 if (acc && at < log_cap) log_put(at, dj, sj);
                 logn += __popc(accmask);
                 log_ok = log_ok && logn <= log_cap;
+                for (uint32_t m = accmask & ~amask; m; m &= m - 1) {
+                    const uint32_t i = __ffs(m) - 1;
+                    if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
+                }
             }
 
             const bool ins = acc && allowed;

@@ -82,7 +82,7 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
             // list-as-queue first (hashed visited table); a query that would overfill the table is redone with the exact
             // bitmap (flag bit1); exact ties switch to usearch's heap mid-flight (flag bit2), or — if the operation log ran
             // out of room — repeat the query with the heap from the start
-            const bool lq_ok = !g.has_deleted && (p.direct & 8) == 0;
+            const bool lq_ok = (p.direct & 8) == 0;
             bool lq = lq_ok, bitmap = false;
             OPCLK(t_q0);
             for (;;) {

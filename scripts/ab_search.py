@@ -28,6 +28,12 @@ def child(args):
     d, nq, k = q_np.shape[1], q_np.shape[0], 10
     ix = gv.Index(d, "l2sq", M=32, M0=64, ef_construction=200, ef_search=64, device=0)
     ix.load(open(f"{TMP}/graph.usearch", "rb").read())
+    step = int(os.environ.get("AB_REMOVE_EVERY", "0"))  # lazy-delete every step-th member before searching
+    if step:
+        import ctypes
+        removed = ctypes.c_uint64(0)
+        for key in range(0, ix.size(), step):
+            gv.lib().gvss_remove(ix._h, key, ctypes.byref(removed))
     dev = torch.device("cuda", 0)
     q = torch.from_numpy(q_np).to(dev)
     okeys = torch.empty((nq, k), dtype=torch.int64, device=dev)

@@ -78,3 +78,39 @@ def test_random_shape_sequential_build_is_the_reference_stream(case, checker):
     ix.add_batch(base)
     ix.flush()
     assert ix.save() == ref.save(), str(case)
+
+
+@pytest.mark.parametrize("case", CASES[:8], ids=lambda c: f"{c['metric']}-d{c['d']}-M{c['M']}-{c['M0']}-n{c['n']}-{'int' if c['integer'] else 'real'}")
+def test_random_shape_with_removed_members_matches_reference(case, checker):
+    """A third of the members removed (lazy delete): they are still traversed — in list-as-queue mode from a side heap —
+    and never returned; ids, distance bits and traversal counters equal the reference's, entry point removed or not."""
+    Checker, kind = checker
+    rng = np.random.default_rng(case["seed"] + 1)
+    n, d = case["n"], case["d"]
+    if case["integer"]:
+        base = rng.integers(0, 3, size=(n, d)).astype(np.float32)
+        q = rng.integers(0, 3, size=(60, d)).astype(np.float32)
+        base[:, 0] += 1.0
+        q[:, 0] += 1.0
+    else:
+        base, q = synth.clustered(n, d, max(4, n // 60), min(6, d), case["seed"] % 1000 + 1, 60)
+    M0 = max(case["M0"], case["M"]) if case["M0"] else 0
+    ref = Checker(d, case["metric"], M=case["M"], M0=M0, ef_construction=40)
+    ref.reserve(n, 1)
+    ref.add_bulk(base, threads=1)
+    ix = gv.Index(d, case["metric"], M=case["M"], M0=M0, ef_construction=40)
+    ix.load(ref.save())
+    gone = rng.choice(n, size=n // 3, replace=False)
+    for key in gone:
+        assert ref.remove(int(key)) == 1
+        assert ix.remove(int(key)) == 1
+    for k, ef in ((1, 1), (3, 5), (10, 17), (10, 64), (10, 200)):
+        want = ref.search_batch(q, k, ef)
+        keys, dist, counts, st = ix.ef_search(q, k, ef, stats=True)
+        msg = f"{case} k={k} ef={ef} ({kind})"
+        np.testing.assert_array_equal(keys, want["keys"], err_msg=msg)
+        np.testing.assert_array_equal(dist.view(np.uint32), want["dist"].view(np.uint32), err_msg=msg)
+        np.testing.assert_array_equal(counts, want["counts"], err_msg=msg)
+        np.testing.assert_array_equal(st["computed"], want["computed"].astype(np.uint32), err_msg=msg)
+        np.testing.assert_array_equal(st["visited"], want["visited"].astype(np.uint32), err_msg=msg)
+        assert not np.isin(keys, gone).any()
