@@ -132,9 +132,9 @@ int gvss_search_device(gvss_index *index, const float *queries, uint64_t nq, uin
  * callers, because cudaMalloc / cudaFree synchronise the whole device. This call runs no cudaMalloc, cudaFree or other
  * allocating routine: the per-query scratch (visited tables, candidate-queue overflow) lives in a 64 MiB array built
  * into the library, which every GPU that loads the library holds until the process exits.
- *  - Limit: one query slot may use at most 1 MiB of the array: 12 bytes per visited-table slot (64*max(ef,k) slots
- *    rounded up to a power of two, at least 4096) plus one bit per graph node — e.g. ef <= 512 on a 4M-node index,
- *    ef <= 1024 on 1M nodes. Beyond that the call fails with an error that states the sizes. When fewer slots fit
+ *  - Limit: one query slot may use at most 1 MiB of the array: 12 bytes per visited-table slot (max(ef,k) * max(M,M0)
+ *    + 2048 slots rounded up to a power of two, at least 4096) plus one bit per graph node — e.g. with M0 = 32: ef <= 512 on
+ *    a 4M-node index, ef <= 1024 on 1M nodes. Beyond that the call fails with an error that states the sizes. When fewer slots fit
  *    than the GPU could run at once, the call is correct but slower than gvss_search_device.
  *  - Rows staged by gvss_add* must have been inserted with gvss_flush beforehand (flushing allocates; this call
  *    refuses instead).
