@@ -8,9 +8,11 @@ A step = one batched search of the 10 000-query batch (k=10) at the smallest ef 
 recall@10 >= 0.95 on the GPU-built graph. `value` is device-timed with queries and index resident in HBM; `e2e` is
 the same batch through the host-pointer C-ABI call (gvss_search: H2D of the queries + kernel + D2H of the results
 inside the timed region). The bulk build (gvss_add_batch_device + gvss_flush) is timed once, before the steps, and
-reported under "build". N > 1: one process per GPU, every rank owns an independent 1M-vector shard (own sub-graph, no
-build-time communication); every query is searched on every shard, per-shard top-k lists are all-gathered over NCCL
-and merged on the device (weak scaling: per-GPU work is fixed).
+reported under "build" with its own roofline (from gvss_get_build_stats) and an end-to-end leg from host memory; the
+exact top-k that provides the ground truth is reported under "exact_topk" with a tensor roofline. N > 1: one process per
+GPU, every rank owns an independent 1M-vector shard (own sub-graph, no build-time communication); every query is
+searched on every shard at shard 0's operating point, the per-shard top-k lists are exchanged through peer memory over
+NVLink and merged by one kernel (fallback: NCCL all-gather + merge), weak scaling: per-GPU work is fixed.
 
 `--impl reference` times the UNMODIFIED reference (vendored usearch via oracle/_ref, else the pinned C port) on the
 host cores on a bounded sample of the same workload.
