@@ -25,7 +25,7 @@ class Info(C.Structure):
     _fields_ = [("size", C.c_uint64), ("capacity", C.c_uint64), ("node_count", C.c_uint64),
                 ("max_level", C.c_uint64), ("memory_usage", C.c_uint64), ("dimensions", C.c_uint64),
                 ("connectivity", C.c_uint32), ("connectivity_base", C.c_uint32), ("expansion_add", C.c_uint32),
-                ("expansion_search", C.c_uint32), ("metric", C.c_char)]
+                ("expansion_search", C.c_uint32), ("metric", C.c_char), ("concurrent_searches_peak", C.c_uint32)]
 
 
 class BuildStats(C.Structure):
@@ -74,11 +74,14 @@ SIGNATURES = {
                                          C.c_void_p, C.c_void_p]),
     "gvss_merge_topk_peers_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                                C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gvss_peer_exchange_status": (C.c_int, [C.POINTER(C.c_uint32)]),
     "gvss_set_build_concurrency": (C.c_int, [C.c_void_p, C.c_uint32]),
     "gvss_last_error": (C.c_char_p, []),
     "gvss_version": (C.c_char_p, []),
     "gvss_kernel_launches": (C.c_uint64, []),
 }
+
+ANY_THREAD = 0xFFFFFFFF  # GVSS_ANY_THREAD
 
 _lib = None
 

@@ -9,6 +9,7 @@
 // shared through shared memory by QT queries per thread.
 #include "kernels.h"
 #include "exact_common.cuh"
+#include <cstdlib>
 #include <vector>
 
 namespace gvss {
@@ -467,8 +468,9 @@ cudaError_t launch_merge_topk(const int64_t *gk, const float *gd, uint32_t shard
 //      of this step are then complete and visible;
 //   3. the lists are merged by (distance, key) like k_merge<1>.
 // Steps must increase by one per call on every rank and result buffers must be double-buffered by the caller (a rank may
-// start step s+1's search while a slow peer still merges step s). A peer that never arrives trips the time-out and the
-// kernel traps instead of hanging the GPU.
+// start step s+1's search while a slow peer still merges step s). A peer that never arrives trips the time-out
+// (GVSS_PEER_TIMEOUT_MS, default 20 s): the merge writes nothing and records the late rank in an error word the host reads
+// with gvss_peer_exchange_status — no trap, the context survives.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr uint32_t kMaxPeers = 16;
 struct PeerLists {
@@ -496,23 +498,37 @@ __device__ __forceinline__ float ld_relaxed_sys_f32(const float *p) {
     return v;
 }
 
+static __device__ unsigned int g_peer_timeouts; // bit r: a merge on this device gave up waiting for rank r
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __global__ void k_merge_peers(PeerLists pl, uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k,
-                              int64_t *__restrict__ keys_out, float *__restrict__ dist_out) {
+                              int64_t *__restrict__ keys_out, float *__restrict__ dist_out, unsigned long long timeout_ns) {
     const uint32_t lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x < shards) {
         __threadfence_system();
         st_release_sys(pl.flags[threadIdx.x] + rank, step);
     }
-    if (lane < shards) {
+    // Wait for the PEERS only. This rank's own lists are complete by stream order, and its own flag slot is written by CTA 0
+    // of this very grid: waiting on it would make every CTA depend on CTA 0 having been scheduled, which CUDA does not
+    // promise once the grid exceeds what the GPU holds at once.
+    bool late = false;
+    if (lane < shards && lane != rank) {
         const uint32_t *mine = pl.flags[rank] + lane;
-        const long long t0 = clock64();
-        // wrap-safe "reached step"; ~4 s at 2 GHz before giving up
-        while ((int32_t)(ld_acquire_sys(mine) - step) < 0) {
-            if (clock64() - t0 > 8000000000ll) { printf("k_merge_peers: rank %u timed out waiting for rank %u at step %u\n", rank, lane, step); __trap(); }
+        const unsigned long long t0 = global_ns();
+        while ((int32_t)(ld_acquire_sys(mine) - step) < 0) { // wrap-safe "reached step"
+            if (global_ns() - t0 > timeout_ns) { late = true; break; }
             __nanosleep(200);
         }
+        if (late) atomicOr(&g_peer_timeouts, 1u << lane);
     }
-    __syncwarp();
+    // a peer that never arrived: no result is written (its list would be stale); the host learns it from
+    // gvss_peer_exchange_status instead of losing the context to a trap
+    if (__ballot_sync(kFull, late)) return;
     const uint64_t q = (uint64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
     if (q >= nq) return;
     const uint32_t total = shards * k;
@@ -568,9 +584,28 @@ cudaError_t launch_merge_topk_peers(const int64_t *const *peer_keys, const float
     }
     const uint32_t wpb = 4;
     const unsigned grid = (unsigned)(((nq ? nq : 1) + wpb - 1) / wpb); // at least CTA 0: the flags must be published even for an empty batch
-    k_merge_peers<<<grid, wpb * 32, 0, st>>>(pl, rank, shards, step, nq, k, keys_out, dist_out);
+    // how long a merge waits for a peer before it gives up (GVSS_PEER_TIMEOUT_MS, default 20 s: a slow shard, a first-call
+    // module load or a reallocation on the peer must not look like a dead rank)
+    static const unsigned long long timeout_ns = [] {
+        const char *e = getenv("GVSS_PEER_TIMEOUT_MS");
+        const unsigned long long ms = e ? strtoull(e, nullptr, 10) : 20000ull;
+        return (ms ? ms : 1ull) * 1000000ull;
+    }();
+    k_merge_peers<<<grid, wpb * 32, 0, st>>>(pl, rank, shards, step, nq, k, keys_out, dist_out, timeout_ns);
     count_launch();
     return cudaGetLastError();
+}
+
+cudaError_t read_peer_timeouts(uint32_t *out) {
+    unsigned int v = 0;
+    cudaError_t e = cudaMemcpyFromSymbol(&v, g_peer_timeouts, sizeof v);
+    if (e != cudaSuccess) return e;
+    if (v) {
+        const unsigned int z = 0;
+        e = cudaMemcpyToSymbol(g_peer_timeouts, &z, sizeof z);
+    }
+    *out = v;
+    return e;
 }
 
 } // namespace gvss

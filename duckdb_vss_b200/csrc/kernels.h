@@ -41,6 +41,9 @@ struct SearchParams {
     uint32_t entry;
     int32_t max_level;
     unsigned long long *work_counter;
+    unsigned long long *fail_word; // optional: receives 1 + the largest index of a query whose candidate queue overflowed
+    uint32_t query_stride;         // floats between queries (0 = dimensions)
+    uint32_t *cluster_out;         // optional: descent-only mode for compact — cluster_out[q] = result of the greedy descent, no beam search
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;
@@ -84,6 +87,8 @@ cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, u
 cudaError_t launch_merge_topk_peers(const int64_t *const *peer_keys, const float *const *peer_dist, uint32_t *const *peer_flags,
                                     uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k, int64_t *keys_out,
                                     float *dist_out, cudaStream_t stream);
+// bit r set = some merge on this device gave up waiting for rank r (read and cleared; synchronises the device)
+cudaError_t read_peer_timeouts(uint32_t *out);
 cudaError_t launch_exact_topk(char metric, const float *base, uint64_t n, const int64_t *keys, const float *queries,
                               uint64_t nq, uint32_t d, uint32_t k, int64_t *ids_out, float *dist_out,
                               cudaStream_t stream);

@@ -65,7 +65,7 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         qi = __shfl_sync(kFull, qi, 0);
         if (qi >= p.nq) break;
 
-        const float *qsrc = p.queries + qi * g.dims;
+        const float *qsrc = p.queries + qi * (p.query_stride ? p.query_stride : g.dims);
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = i < g.dims ? __ldg(qsrc + i) : 0.0f;
         __syncwarp();
         if (METRIC == kCos && w.g4) w.q_a2 = fold_a2(w.q, g.dpad);
@@ -76,6 +76,12 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
 #if GVSS_OPCOUNT
         for (int i = 0; i < kOpCount; i++) w.opc[i] = i == kOpQueries ? 1ull : 0ull;
 #endif
+        if (p.cluster_out) { // compact (index.hpp:3043-3046): only the node the descent through levels max_level..1 ends at
+            const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            if (lane == 0) p.cluster_out[qi] = closest;
+            __syncwarp();
+            continue;
+        }
         if (g.count && p.k) {
             const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
             const Counters before = cnt;
@@ -108,6 +114,7 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         if (lane == 0) for (int i = 0; i < kOpCount; i++) atomicAdd(&g_opcount[i], w.opc[i]);
 #endif
         if (lane == 0) {
+            if ((cnt.flags & 1u) && p.fail_word) atomicMax(p.fail_word, qi + 1ull);
             if (p.counts_out) p.counts_out[qi] = n;
             if (p.stats_out) p.stats_out[qi] = gvss_search_stats{cnt.computed, cnt.cycles, cnt.base, cnt.flags & 0x7FFFFFFFu};
         }

@@ -36,6 +36,7 @@ class Index:
         capi.check(capi.lib().gvss_reserve(self._h, int(members), int(threads)))
 
     def add(self, key, vec, thread=0):
+        """``index.add(key, vec, thread)``; ``thread=capi.ANY_THREAD`` is ``index_dense_t::any_thread()``."""
         vec = np.ascontiguousarray(vec, dtype=np.float32)
         assert vec.size == self.dims
         capi.check(capi.lib().gvss_add(self._h, int(key), _ptr(vec), int(thread)))

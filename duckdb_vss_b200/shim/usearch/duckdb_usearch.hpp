@@ -83,6 +83,7 @@ template <typename key_at = std::int64_t> class index_dense_gt {
     gvss_index *handle_ = nullptr;
     metric_punned_t metric_{};
     index_dense_config_t config_{};
+    std::string create_error_; // why make() failed (the thread that calls add() later has no message of its own)
 
     static std::string last_error() { return std::string(gvss_last_error()); }
 
@@ -143,6 +144,7 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         std::swap(handle_, o.handle_);
         std::swap(metric_, o.metric_);
         std::swap(config_, o.config_);
+        std::swap(create_error_, o.create_error_);
     }
 
     // index_dense_gt::make(metric, config) (hnsw_index.cpp:189). A failed creation leaves an index whose calls fail.
@@ -158,7 +160,8 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         c.expansion_add = (uint32_t)config.expansion_add;
         c.expansion_search = (uint32_t)config.expansion_search;
         c.device = -1;
-        if (metric.scalar_kind() != scalar_kind_t::f32_k || gvss_create(&c, &r.handle_)) r.handle_ = nullptr;
+        if (metric.scalar_kind() != scalar_kind_t::f32_k) r.create_error_ = "only f32 vectors are supported";
+        else if (gvss_create(&c, &r.handle_)) { r.create_error_ = last_error(); r.handle_ = nullptr; }
         return r;
     }
     explicit operator bool() const noexcept { return handle_ != nullptr; }
@@ -169,15 +172,15 @@ template <typename key_at = std::int64_t> class index_dense_gt {
 
     add_result_t add(vector_key_t key, const float *vector, std::size_t thread = any_thread(), bool = true) {
         add_result_t r;
-        if (!handle_) { r.error.message = "index was not created: " + last_error(); return r; }
-        if (gvss_add(handle_, (int64_t)key, vector, thread == any_thread() ? 0u : (uint32_t)thread)) r.error.message = last_error();
+        if (!handle_) { r.error.message = "index was not created: " + create_error_; return r; }
+        if (gvss_add(handle_, (int64_t)key, vector, thread == any_thread() ? GVSS_ANY_THREAD : (uint32_t)thread)) r.error.message = last_error();
         return r;
     }
 
     // the only search entry the extension uses (index_dense.hpp:619-623)
     search_result_t ef_search(const float *query, std::size_t wanted, std::size_t ef, std::size_t = any_thread(), bool = false) const {
         search_result_t r;
-        if (!handle_) { r.error.message = "index was not created"; return r; }
+        if (!handle_) { r.error.message = "index was not created: " + create_error_; return r; }
         if (!wanted) return r;
         r.keys_.resize(wanted);
         r.distances_.resize(wanted);

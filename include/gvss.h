@@ -11,10 +11,16 @@
  *   - pointers are HOST memory unless the function name ends in `_device`;
  *   - there is no CPU fallback: with no CUDA device every compute entry point fails with an error.
  *
- * Threading (mirrors how the extension calls usearch): gvss_add may be called from
- * `host_threads` threads at once with distinct thread ids (PhysicalCreateHNSWIndex,
- * hnsw_index_physical_create.cpp:144-205); gvss_search* may run concurrently with other searches
- * (shared side of HNSWIndex::rwlock); everything else is called with the exclusive side held.
+ * Threading (mirrors how the extension calls usearch):
+ *   - gvss_add may be called from `host_threads` threads at once, each with its own thread id 0..host_threads-1
+ *     (PhysicalCreateHNSWIndex, hnsw_index_physical_create.cpp:144-205), and from any number of threads with
+ *     GVSS_ANY_THREAD (HNSWIndex::Construct under the SHARED side of HNSWIndex::rwlock, hnsw_index.cpp:433-447) — also
+ *     while searches run: a row is only staged, behind a per-buffer mutex, and enters the graph in the next flush;
+ *   - gvss_search / gvss_search_device / gvss_save / gvss_get_* hold the index's reader lock: calls from different host
+ *     threads run concurrently, each gvss_search on a stream and scratch buffer of its own;
+ *   - everything that changes the graph (flush — explicit or triggered by a search that finds staged rows —, remove,
+ *     compact, reserve, reset, load) takes the writer lock and waits for running searches. The library does its own
+ *     locking: no call sequence from any number of threads corrupts the index.
  */
 #ifndef GVSS_H
 #define GVSS_H
@@ -31,6 +37,7 @@ extern "C" {
 #define GVSS_METRIC_IP 'i'   /* metric_kind_t::ip_k  */
 
 #define GVSS_FREE_KEY INT64_MAX /* key written into removed nodes, index_dense.hpp:1246-1250 */
+#define GVSS_ANY_THREAD 0xFFFFFFFFu /* index_dense_t::any_thread(), hnsw_index.cpp:485,497: "whichever thread I am" */
 
 typedef struct gvss_index gvss_index;
 
@@ -60,6 +67,7 @@ typedef struct gvss_info {
     uint64_t dimensions;   /* index.dimensions(), hnsw_index.cpp:216 */
     uint32_t connectivity, connectivity_base, expansion_add, expansion_search;
     char metric;           /* index.metric().metric_kind(), hnsw_index.cpp:220 */
+    uint32_t concurrent_searches_peak; /* most gvss_search calls that were in flight on the GPU at the same time so far */
 } gvss_info;
 
 /* per-query traversal counters, same meaning as usearch's search_result_t (index.hpp:2187-2192) */
@@ -86,9 +94,10 @@ int gvss_reserve(gvss_index *index, uint64_t members, uint32_t host_threads);
 /* --- construction ------------------------------------------------------------------------------------------- */
 /* index.add(key, vec, thread), hnsw_index_physical_create.cpp:184 and hnsw_index.cpp:443. Copies `vec` before
  * returning; only stages the row (graph work happens in gvss_flush or the next call that needs a consistent
- * graph). Fails with "Reserve capacity ahead of insertions!" (index.hpp:2332-2335) when full and with
- * "Duplicate keys not allowed in high-level wrappers" (index_dense.hpp:1752-1753) is NOT checked, like the
- * extension's configuration (enable_key_lookups=false makes contains() always false). */
+ * graph). host_thread: an id below the thread count given to gvss_reserve, or GVSS_ANY_THREAD; any other value is an
+ * error. Fails with "Reserve capacity ahead of insertions!" (index.hpp:2332-2335) when full. Duplicate keys are NOT
+ * rejected ("Duplicate keys not allowed in high-level wrappers", index_dense.hpp:1752-1753, never fires in the
+ * extension either: enable_key_lookups=false makes contains() always false). */
 int gvss_add(gvss_index *index, int64_t key, const float *vec, uint32_t host_thread);
 /* n rows, row-major n×dimensions — the layout HNSWIndex::Construct already has after Flatten (hnsw_index.cpp:399-406) */
 int gvss_add_batch(gvss_index *index, const int64_t *keys, const float *vecs, uint64_t n);
@@ -104,7 +113,9 @@ int gvss_flush(gvss_index *index);
 int gvss_set_build_concurrency(gvss_index *index, uint32_t max_concurrent_inserts);
 /* index.remove(key), hnsw_index.cpp:478: lazy delete (index_dense.hpp:1228-1255); unknown key: *removed = 0. */
 int gvss_remove(gvss_index *index, int64_t key, uint64_t *removed);
-/* index.compact(), hnsw_index.cpp:458 */
+/* index.compact(), hnsw_index.cpp:458 = index_gt::compact (index.hpp:3007-3096): re-orders the nodes by (level descending,
+ * nearest upper-level node ascending) and renames every link; removed members are kept (this usearch version does not
+ * drop them). The stream saved afterwards equals the reference's after its compact(), byte for byte. */
 int gvss_compact(gvss_index *index);
 /* Deleting compaction (the extension's README.md:69 says PRAGMA hnsw_compact_index prunes deleted
  * items; index_gt::compact in this usearch version, index.hpp:3007-3096, only re-orders and keeps them): builds a fresh graph
@@ -193,12 +204,17 @@ int gvss_merge_topk_device(const int64_t *gathered_keys, const float *gathered_d
  * over NVLink and the ranks synchronise through flags in peer memory (no reference counterpart).
  * peer_keys[s] / peer_dist[s]: shard s's result buffers as mapped into THIS process (CUDA IPC / symmetric memory; entry
  * [rank] is the local buffer); peer_flags[s]: shard s's flag array (16 zero-initialised u32). All three are HOST arrays
- * of `shards` device pointers. Call it on every rank, after that rank's search on the same stream, with the same `step`
+ * of `shards` device pointers. Call it on every rank, after that rank's search in stream order, with the same `step`
  * = 1, 2, 3, ... ; the caller alternates between two sets of result buffers from step to step. shards <= 16,
- * shards * k <= 256. A rank that never arrives makes the others trap after ~4 s instead of hanging. */
+ * shards * k <= 256. A rank that does not arrive within GVSS_PEER_TIMEOUT_MS (environment, default 20000) makes the
+ * others skip the merge of that step (outputs untouched) and record it: see gvss_peer_exchange_status. */
 int gvss_merge_topk_peers_device(const int64_t *const *peer_keys, const float *const *peer_dist, uint32_t *const *peer_flags,
                                  uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k, int64_t *keys_out,
                                  float *dist_out, void *cuda_stream);
+
+/* Bit r of *timed_out is set when a gvss_merge_topk_peers_device launch on the current device gave up waiting for rank r
+ * since the last call (the word is cleared by the call; it synchronises the device). 0 = every merge so far was complete. */
+int gvss_peer_exchange_status(uint32_t *timed_out);
 
 /* --- misc ---------------------------------------------------------------------------------------------------- */
 const char *gvss_last_error(void);

@@ -37,6 +37,8 @@ def lib():
         L.ref_duckdb_distance.restype = C.c_float
         L.ref_duckdb_distance.argtypes = [C.c_char, f32p, f32p, u32]
         L.ref_duckdb_topk.argtypes = [C.c_char, f32p, u64, f32p, u64, u32, u32, u32, i64p, f32p]
+        L.ref_fast_topk.argtypes = [C.c_char, f32p, u64, f32p, u64, u32, u32, u32, i64p, f32p]
+        L.ref_compact.argtypes = [vp]
         L.ref_hardware_threads.restype = u32
         _lib = L
     return _lib
@@ -142,6 +144,11 @@ class RefIndex:
         if lib().ref_load(self.h, buf.ctypes.data_as(C.POINTER(C.c_uint8)), buf.size):
             raise RuntimeError("reference load failed")
 
+    def compact(self):
+        """index.compact() (hnsw_index.cpp:458): re-orders the nodes, keeps removed members."""
+        if lib().ref_compact(self.h):
+            raise RuntimeError("reference compact failed")
+
 
 def metric(kind, a, b):
     a = np.ascontiguousarray(a, dtype=np.float32)
@@ -162,4 +169,15 @@ def duckdb_topk(kind, base, qs, k, threads=1):
     dist = np.empty((qs.shape[0], k), dtype=np.float32)
     lib().ref_duckdb_topk(METRIC_CHAR[kind], _f32p(base), base.shape[0], _f32p(qs), qs.shape[0], base.shape[1], k,
                           threads, _i64p(ids), _f32p(dist))
+    return ids, dist
+
+
+def fast_topk(kind, base, qs, k, threads=1):
+    """Ground truth at full size: vectorised candidate ranking + exact re-score with DuckDB's folds, (distance, rowid) order."""
+    base = np.ascontiguousarray(base, dtype=np.float32)
+    qs = np.ascontiguousarray(qs, dtype=np.float32)
+    ids = np.empty((qs.shape[0], k), dtype=np.int64)
+    dist = np.empty((qs.shape[0], k), dtype=np.float32)
+    lib().ref_fast_topk(METRIC_CHAR[kind], _f32p(base), base.shape[0], _f32p(qs), qs.shape[0], base.shape[1], k,
+                        threads, _i64p(ids), _f32p(dist))
     return ids, dist

@@ -17,7 +17,9 @@
 #include "usearch/duckdb_usearch.hpp"
 #include "core_functions/array_kernels.hpp"
 
+#include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <chrono>
 #include <cstdint>
 #include <cstring>
@@ -240,6 +242,74 @@ void ref_duckdb_topk(char metric, const float *base, uint64_t n, const float *qs
         for (uint32_t t = 0; t < threads; t++) ts.emplace_back(work, t);
         for (auto &t : ts) t.join();
     }
+}
+
+// index.compact() as HNSWIndex::Compact calls it (hnsw_index.cpp:451-464 -> index_dense.hpp:1479-1496 -> index.hpp:3007-3096)
+int ref_compact(void *p) {
+    auto *h = static_cast<ref_handle *>(p);
+    auto r = h->index.compact();
+    if (!r) { r.error.release(); return 1; }
+    return 0;
+}
+
+// Ground truth for recall at full size (10k queries x 1M rows is minutes of work for the sequential folds above): candidates
+// are ranked with SSE-width partial sums (4 queries per pass over a row, any summation order), the best k + 16 of each query
+// are then re-scored with DuckDB's exact fold and ordered by (distance, rowid) — the same final comparator as
+// ref_duckdb_topk. Not a product path and not a timed baseline: it only tells the reference arm of bench.py its recall.
+void ref_fast_topk(char metric, const float *base, uint64_t n, const float *qs, uint64_t nq, uint32_t d, uint32_t k,
+                   uint32_t threads, int64_t *ids_out, float *dist_out) {
+    typedef float v4 __attribute__((vector_size(16)));
+    if (!threads) threads = 1;
+    const uint32_t kc = k + 16, d4 = d / 4;
+    std::atomic<uint64_t> cursor{0};
+    auto work = [&]() {
+        std::vector<std::pair<float, int64_t>> heap[4], fin;
+        for (;;) {
+            const uint64_t q0 = cursor.fetch_add(4);
+            if (q0 >= nq) break;
+            const uint32_t nqq = (uint32_t)std::min<uint64_t>(4, nq - q0);
+            for (auto &hp : heap) hp.clear();
+            for (uint64_t i = 0; i < n; i++) {
+                const float *b = base + i * d;
+                float sc[4];
+                for (uint32_t j = 0; j < nqq; j++) {
+                    const float *q = qs + (q0 + j) * d;
+                    v4 ab = {0, 0, 0, 0}, a2 = ab, b2 = ab;
+                    for (uint32_t t = 0; t < d4; t++) {
+                        v4 x, y;
+                        std::memcpy(&x, q + 4 * t, 16); std::memcpy(&y, b + 4 * t, 16);
+                        if (metric == 'e') { const v4 df = x - y; ab += df * df; }
+                        else { ab += x * y; if (metric == 'c') { a2 += x * x; b2 += y * y; } }
+                    }
+                    float sab = ab[0] + ab[1] + ab[2] + ab[3], sa2 = a2[0] + a2[1] + a2[2] + a2[3], sb2 = b2[0] + b2[1] + b2[2] + b2[3];
+                    for (uint32_t t = d4 * 4; t < d; t++) {
+                        if (metric == 'e') sab += (q[t] - b[t]) * (q[t] - b[t]);
+                        else { sab += q[t] * b[t]; sa2 += q[t] * q[t]; sb2 += b[t] * b[t]; }
+                    }
+                    sc[j] = metric == 'e' ? sab : metric == 'i' ? -sab : 1.0f - sab / std::sqrt(sa2 * sb2);
+                }
+                for (uint32_t j = 0; j < nqq; j++) {
+                    auto &hp = heap[j];
+                    std::pair<float, int64_t> e(sc[j], (int64_t)i);
+                    if (hp.size() < kc) { hp.push_back(e); std::push_heap(hp.begin(), hp.end()); }
+                    else if (e < hp.front()) { std::pop_heap(hp.begin(), hp.end()); hp.back() = e; std::push_heap(hp.begin(), hp.end()); }
+                }
+            }
+            for (uint32_t j = 0; j < nqq; j++) {
+                fin.clear();
+                for (auto &e : heap[j]) fin.emplace_back(ref_duckdb_distance(metric, base + (uint64_t)e.second * d, qs + (q0 + j) * d, d), e.second);
+                std::sort(fin.begin(), fin.end());
+                for (uint32_t t = 0; t < k; t++) {
+                    ids_out[(q0 + j) * k + t] = t < fin.size() ? fin[t].second : -1;
+                    if (dist_out) dist_out[(q0 + j) * k + t] = t < fin.size() ? fin[t].first : INFINITY;
+                }
+            }
+        }
+    };
+    std::vector<std::thread> ts;
+    for (uint32_t t = 1; t < threads; t++) ts.emplace_back(work);
+    work();
+    for (auto &t : ts) t.join();
 }
 
 uint32_t ref_hardware_threads(void) { return std::thread::hardware_concurrency(); }

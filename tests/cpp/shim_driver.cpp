@@ -85,5 +85,34 @@ int main() {
                 (int)(bool)lr, loaded.size(), (int)(ids3 == ids2));
     index.reset();                                                // hnsw_index.cpp:384
     std::printf("after_reset_size %zu\n", index.size());
+
+    // INSERT while scans run: HNSWIndex::Construct adds with any_thread() under the SHARED side of rwlock
+    // (hnsw_index.cpp:433-447), so adds and ef_search calls of other connections overlap. Nothing may be lost.
+    index.reserve({2048, T});
+    std::atomic<bool> stop{false};
+    std::atomic<int> bad{0};
+    std::thread scanner([&] {
+        while (!stop.load()) {
+            auto r = index.ef_search(q, 3, 64);
+            if (!r) bad++;
+        }
+    });
+    std::vector<std::thread> writers;
+    for (size_t t = 0; t < 2; t++)
+        writers.emplace_back([&, t] {
+            for (size_t i = t; i < n; i += 2) {
+                const auto result = index.add((row_t)(5000 + i), rows.data() + 3 * i, USearchIndexType::any_thread());
+                if (!result) bad++;
+            }
+        });
+    for (auto &w : writers) w.join();
+    stop = true;
+    scanner.join();
+    auto r4 = index.ef_search(q, 1, 64);
+    std::vector<row_t> ids4(r4.size());
+    r4.dump_to(ids4.data());
+    std::printf("concurrent_insert_scan failures %d size %zu nearest %lld\n", bad.load(), index.size(), ids4.empty() ? -1ll : (long long)ids4[0]);
+    const auto wrong_thread = index.add(1, rows.data(), 99);      // thread id beyond reserve({n, T}): refused, not aliased
+    std::printf("thread_out_of_range_refused %d\n", (int)!wrong_thread);
     return 0;
 }

@@ -25,6 +25,8 @@ def test_shim_driver_behaves_like_the_reference_index(tmp_path):
     m = re.search(r"stream_bytes (\d+) serialized_length (\d+) load_ok 1 reloaded_size 728 same_results 1", out)
     assert m and m.group(1) == m.group(2)
     assert "after_reset_size 0" in out
+    assert "concurrent_insert_scan failures 0 size 729 nearest 5011" in out   # row (1,2,3) is grid row 11
+    assert "thread_out_of_range_refused 1" in out
 
 
 def test_multi_scan_prefetch_serves_the_index_join_from_one_batched_search(tmp_path):
