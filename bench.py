@@ -1,21 +1,28 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the HNSW hot path (BASELINE.json: "HNSW search QPS at recall@10>=0.95 (batched) +
-index build vectors/sec" on configs[1] = 1M x FLOAT[128] l2sq, 10k-query batch, k=10).
+index build vectors/sec").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl gvss|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl gvss|reference] [--workload sift1m|deep10m]
 
-A step = one batched search of the 10 000-query batch (k=10) at the smallest ef of the sweep that reaches
-recall@10 >= 0.95 on the GPU-built graph. `value` is device-timed with queries and index resident in HBM; `e2e` is
-the same batch through the host-pointer C-ABI call (gvss_search: H2D of the queries + kernel + D2H of the results
-inside the timed region). The bulk build (gvss_add_batch_device + gvss_flush) is timed once, before the steps, and
-reported under "build" with its own roofline (from gvss_get_build_stats) and an end-to-end leg from host memory; the
-exact top-k that provides the ground truth is reported under "exact_topk" with a tensor roofline. N > 1: one process per
-GPU, every rank owns an independent 1M-vector shard (own sub-graph, no build-time communication); every query is
-searched on every shard at shard 0's operating point, the per-shard top-k lists are exchanged through peer memory over
-NVLink and merged by one kernel (fallback: NCCL all-gather + merge), weak scaling: per-GPU work is fixed.
+Default workload = configs[1]: 1M x FLOAT[128] l2sq, 10 000-query batch, k=10. A step = one batched search of the whole
+query batch at the smallest ef of the sweep whose recall@10 is >= 0.95. `value` is device-timed with queries and index
+resident in HBM; `e2e` is the same step from HOST buffers (H2D of the queries, search, merge, D2H of the result list inside
+the timed region). The bulk build (gvss_add_batch_device + gvss_flush) is timed once, before the steps, and reported under
+"build" with its own roofline (from gvss_get_build_stats); the exact top-k that provides the ground truth is reported
+under "exact_topk".
 
-`--impl reference` times the UNMODIFIED reference (vendored usearch via oracle/_ref, else the pinned C port) on the
-host cores on a bounded sample of the same workload.
+N > 1 (one process per GPU, torchrun):
+  * --workload sift1m (default, weak scaling): every rank owns an independent 1M-vector shard (own sub-graph, no build-time
+    communication). Every query is searched on every shard; the per-shard top-k lists are exchanged through peer memory over
+    NVLink and merged by one kernel on a second stream, so the merge of step s overlaps the search of step s+1 (fallback:
+    NCCL all-gather + merge). ef is chosen on the recall of the MERGED list against the exact top-k over the union of all
+    shards. `value` counts per-shard query searches summed over ranks; config.global_queries_per_s is the batch rate.
+  * --workload deep10m (configs[3], strong scaling): ONE 10M x FLOAT[96] ip set partitioned over the N GPUs by contiguous
+    row ranges; `value` = queries answered per second by the whole job (every query answered once, from all shards).
+
+`--impl reference` times the UNMODIFIED reference (vendored usearch via oracle/_ref) on the host cores on the SAME config:
+the full 1M-vector index built by all host threads with the extension's pattern, all 10 000 queries per step, at the
+smallest ef of the same sweep at which the REFERENCE-built graph reaches recall@10 >= 0.95.
 """
 import argparse
 import ctypes
@@ -32,12 +39,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "hnsw_search_qps_at_recall10_ge_0.95"
-EF_SWEEP = (16, 32, 64, 128, 192, 256, 288, 320, 384, 512)
+EF_SWEEP = (16, 32, 64, 96, 128, 160, 192, 224, 256, 288, 320, 384, 512)
 # with the usearch defaults (M=16, efc=128) recall@10 >= 0.95 is NOT reachable on the 1M set within
 # ef <= 512 (reference-built graph: 0.80 at ef=512, profiles/recall_1m_r1.txt), so both arms use M=32 / ef_construction=200.
 M_BENCH, M0_BENCH, EFC_BENCH = 32, 64, 200
-REF_EF = 288  # smallest ef of the sweep at which the 1M workload reaches recall@10 >= 0.95 (0.952; 256 gives 0.946 on both
-              # builders' graphs); used by the bounded reference arm
+WORKLOADS = {
+    # name: (label, metric, dims, vectors, generator note)
+    "sift1m": ("1M x FLOAT[128] l2sq (SIFT-1M shape), 10k-query batch, k=10", "l2sq", 128, 1_000_000,
+               "clustered(C=N/100, r=16) seed 42 (SURVEY.md App. D law, numpy)"),
+    "deep10m": ("10M x FLOAT[96] ip (Deep10M shape) partitioned over the GPUs, 10k-query batch, k=10", "ip", 96, 10_000_000,
+                "clustered(C=N/100, r=24) seed 46, L2-normalised (SURVEY.md §8d config 4, numpy)"),
+}
 
 
 def peaks():
@@ -103,57 +115,76 @@ def algorithmic_bytes(stats, d, M, M0, k):
     return c * 4 * d + h0 * (4 + 4 * M0) + hup * (4 + 4 * M) + stats.shape[0] * 12.0 * k
 
 
+def make_data(workload, n_total, nq):
+    """(base[n_total, d], queries[nq, d]) of the named workload, deterministic."""
+    from duckdb_vss_b200 import synth
+    if workload == "deep10m":
+        c = synth.config("deep10m", n=n_total, nq=nq)
+        return c["base"], c["queries"]
+    return synth.clustered(n_total, 128, max(1024, n_total // 100), 16, 42, nq)
+
+
 def run_reference(args):
-    """CPU arm: the reference's own usearch path on the host cores (bounded sample)."""
+    """CPU arm: the reference's own usearch path on the host cores, on the same config as the GPU arm at N=1."""
     import oracle
     from duckdb_vss_b200 import synth
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    label, metric, d, n_default, gen = WORKLOADS["sift1m"]
+    n = args.n or n_default
+    nq, k = args.nq, 10
     if oracle.have_ref():
         from oracle import ref as impl
         kind, Index, threads = "reference", impl.RefIndex, impl.hardware_threads()
-    else:
+    else:  # reference sources absent and no prebuilt oracle/_ref: the pinned C port on a sample it can finish
         oracle.build()
         from oracle import port as impl
         kind, Index, threads = "port", impl.PortIndex, 1
-    # bounded sample: the CPU build of the full 1M set takes ~130 s on 16 cores, so the index covers the first 16k x cores
-    # vectors (the whole set from 64 cores up). ef is NOT re-tuned on that smaller index: it stays at the operating point
-    # the 1M workload needs for recall@10 >= 0.95 (REF_EF on both reference-built and GPU-built graphs,
-    # profiles/recall_1m_r1.txt), so a step costs the CPU what a step of the real workload costs (minus the log N of hops).
-    n_sample = args.ref_n or min(args.n, max(20000, 16000 * threads))
-    nq = min(args.nq, 2000 if kind == "reference" else 200)
-    base, q = synth.clustered(n_sample, args.dims, max(1024, n_sample // 100), 16, 42, nq)
-    ix = Index(args.dims, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
-    ix.reserve(n_sample, threads)
+        n, nq = min(n, 20000), min(nq, 200)
+    base, q = make_data("sift1m", n, nq)
+    ix = Index(d, metric, M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
+    ix.reserve(n, threads)
     t0 = time.perf_counter()
-    ix.add_bulk(base, threads=threads)
+    ix.add_bulk(base, threads=threads)   # T threads, shared 2048-row chunk cursor (hnsw_index_physical_create.cpp:144-205)
     t_build = time.perf_counter() - t0
-    ef, recall = args.ef or REF_EF, None
+    t0 = time.perf_counter()
     if kind == "reference":
-        truth, _ = impl.duckdb_topk("l2sq", base, q[:200], 10, threads=threads)
-        recall = synth.recall_at_k(ix.search_batch(q[:200], 10, ef, threads=threads)["keys"], truth)
+        truth, _ = impl.fast_topk(metric, base, q, k, threads=threads)
+    else:
+        truth, _ = impl.exact_topk(metric, base, q, k)
+    t_truth = time.perf_counter() - t0
+    sweep, ef, recall = {}, args.ef, None
+    for e in ([args.ef] if args.ef else EF_SWEEP):
+        r = synth.recall_at_k(ix.search_batch(q, k, e, threads=threads)["keys"], truth)
+        sweep[e] = round(r, 4)
+        ef, recall = e, r
+        if r >= 0.95:
+            break
     for _ in range(args.warmup):
-        ix.search_batch(q, 10, ef, threads=threads)
+        ix.search_batch(q, k, ef, threads=threads)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ix.search_batch(q, 10, ef, threads=threads)
+        ix.search_batch(q, k, ef, threads=threads)
     dt = time.perf_counter() - t0
     qps = nq * args.steps / dt
-    sample = f"index over the first {n_sample} of {args.n} vectors built by {threads} host threads; {nq} of {args.nq} queries per step; ef={ef}"
+    sample = (f"the whole workload: index over all {n} vectors built by {threads} host threads in {t_build:.0f} s, all {nq} queries per "
+              f"step, ef={ef} = smallest ef of the sweep with recall@10 >= 0.95 on the reference-built graph (ground truth: "
+              f"vectorised CPU scan + exact re-score, {t_truth:.0f} s, untimed)")
     line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "1M x FLOAT[128] l2sq (SIFT-1M shape), 10k-query batch, k=10", "ef_search": ef,
-                       "recall_at_10": recall, "M": M_BENCH, "M0": M0_BENCH, "ef_construction": EFC_BENCH},
+            "config": {"workload": label, "generator": gen, "n_per_gpu": n, "queries_per_step": nq, "k": k, "ef_search": ef,
+                       "recall_at_10": recall, "ef_sweep": sweep, "M": M_BENCH, "M0": M0_BENCH, "ef_construction": EFC_BENCH,
+                       "note": "the CPU arm runs the N=1 workload whatever --gpus says (host cores do not grow with the GPU count)"},
             "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": threads, "kind": kind, "sample": sample,
-                             "build_vectors_per_s": n_sample / t_build},
+                             "build_vectors_per_s": n / t_build},
             "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "build": {"value": n_sample / t_build, "unit": "vectors/s", "vectors": n_sample, "seconds": t_build}}
+            "build": {"value": n / t_build, "unit": "vectors/s", "vectors": n, "seconds": t_build}}
     print(json.dumps(line))
 
 
-def cpu_baseline(args, blob_getter, q, ef, truth, gpu_keys=None):
+def cpu_baseline(args, d, metric, blob_getter, q, ef, truth, gpu_keys=None):
     """Reference usearch (oracle/_ref) on the host cores: search on the SAME (GPU-built) graph, build on a bounded sample."""
     try:
         import oracle
@@ -167,7 +198,7 @@ def cpu_baseline(args, blob_getter, q, ef, truth, gpu_keys=None):
             from oracle import port as impl
             kind, threads, Index = "port", 1, impl.PortIndex
         from duckdb_vss_b200 import synth
-        ix = Index(args.dims, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
+        ix = Index(d, metric, M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
         t0 = time.perf_counter()
         ix.load(blob_getter())
         t_load = time.perf_counter() - t0
@@ -178,17 +209,17 @@ def cpu_baseline(args, blob_getter, q, ef, truth, gpu_keys=None):
         dt = time.perf_counter() - t0
         rec = synth.recall_at_k(r["keys"], truth[:nq])
         ids_same = bool(gpu_keys is not None and np.array_equal(r["keys"], gpu_keys[:nq]))
-        # build sample: first min(n, 2500*T) vectors with the extension's thread pattern
-        nb = min(args.n, max(20000, 1500 * threads)) if kind == "reference" else 3000
-        base_s, _ = synth.clustered(nb, args.dims, max(1024, nb // 100), 16, 42, 0)
-        b = Index(args.dims, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
+        # build sample: a prefix of the set with the extension's thread pattern (the full build is what --impl reference times)
+        nb = min(args.n or 10 ** 9, max(20000, 1500 * threads)) if kind == "reference" else 3000
+        base_s, _ = make_data("sift1m", nb, 0)
+        b = Index(128, "l2sq", M=M_BENCH, M0=M0_BENCH, ef_construction=EFC_BENCH)
         b.reserve(nb, threads)
         t0 = time.perf_counter()
         b.add_bulk(base_s, threads=threads)
         tb = time.perf_counter() - t0
         return {"value": nq / dt, "unit": "queries/s", "cores": threads, "kind": kind,
-                "sample": f"{nq} queries, ef={ef}, on the GPU-built 1M graph loaded from its usearch stream (load {t_load:.1f}s); "
-                          f"build timed on the first {nb} vectors", "recall_at_10": rec,
+                "sample": f"{nq} queries, ef={ef}, on the GPU-built graph loaded from its usearch stream (load {t_load:.1f}s); "
+                          f"build timed on the first {nb} vectors of the 1M x 128 set", "recall_at_10": rec,
                 "ids_identical_to_gpu_on_same_graph": ids_same,
                 "build_vectors_per_s": nb / tb}
     except Exception as e:  # the baseline must never take the product number down
@@ -201,11 +232,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gvss", choices=["gvss", "reference"])
-    ap.add_argument("--vectors", dest="n", type=int, default=1_000_000, help="base vectors per GPU")
+    ap.add_argument("--workload", default="sift1m", choices=sorted(WORKLOADS))
+    ap.add_argument("--vectors", dest="n", type=int, default=0, help="base vectors (per GPU for sift1m, in total for deep10m); 0 = the config's size")
     ap.add_argument("--nq", type=int, default=10_000)
-    ap.add_argument("--dims", type=int, default=128)
     ap.add_argument("--ef", type=int, default=0, help="0 = smallest ef of the sweep with recall@10 >= 0.95")
-    ap.add_argument("--ref-n", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "gvss" else args.warmup
@@ -216,6 +246,7 @@ def main():
     import torch.distributed as dist
     import duckdb_vss_b200 as gv
     from duckdb_vss_b200 import synth, index as gvi
+    from duckdb_vss_b200.sharded import shard_range
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -228,18 +259,33 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    d, n, nq, k, M, M0 = args.dims, args.n, args.nq, 10, M_BENCH, M0_BENCH
-    # per-rank shard: same law, shard-specific seed; the query batch is identical on every rank (seed 43 stream of rank 0)
-    base_np, q_np = synth.clustered(n, d, max(1024, n // 100), 16, 42 + 1000 * rank, 0)
-    _, q_np = synth.clustered(1, d, max(1024, n // 100), 16, 42, nq)
+    label, metric, d, n_default, gen = WORKLOADS[args.workload]
+    strong = args.workload == "deep10m"
+    nq, k, M, M0 = args.nq, 10, M_BENCH, M0_BENCH
+    if strong:
+        # ONE set partitioned by contiguous row ranges; keys = global row numbers
+        n_total = args.n or n_default
+        base_all, q_np = make_data(args.workload, n_total, nq)
+        lo, hi = shard_range(n_total, rank, world)
+        base_np = np.ascontiguousarray(base_all[lo:hi])
+        del base_all
+        n = hi - lo
+        keys_np = np.arange(lo, hi, dtype=np.int64)
+    else:
+        # weak scaling: per-rank shard of the same law (shard-specific seed), the query batch identical on every rank
+        n = args.n or n_default
+        n_total = n * world
+        base_np, _ = synth.clustered(n, d, max(1024, n // 100), 16, 42 + 1000 * rank, 0)
+        _, q_np = synth.clustered(1, d, max(1024, n // 100), 16, 42, nq)
+        keys_np = np.arange(n, dtype=np.int64) + rank * n
     base = torch.from_numpy(base_np).to(dev)
     q = torch.from_numpy(q_np).to(dev)
-    stream = torch.cuda.current_stream().cuda_stream
+    s_search = torch.cuda.current_stream()
+    stream = s_search.cuda_stream
 
     # ---- bulk build (timed once): rows already in HBM -> graph ------------------------------------------------
-    ix = gv.Index(d, "l2sq", M=M, M0=M0, ef_construction=EFC_BENCH, ef_search=64, device=local)
+    ix = gv.Index(d, metric, M=M, M0=M0, ef_construction=EFC_BENCH, ef_search=64, device=local)
     ix.reserve(n, 1)
-    keys_np = np.arange(n, dtype=np.int64) + rank * n
     torch.cuda.synchronize()
     l0 = gv.lib().gvss_kernel_launches()
     t0 = time.perf_counter()
@@ -253,64 +299,79 @@ def main():
     build_bytes = (bst["query_distances"] * 4.0 * d + bst["pair_distances"] * 8.0 * d + bst["base_expansions"] * (4 + 4.0 * M0)
                    + bst["upper_expansions"] * (4 + 4.0 * M) + bst["rows_written"] * (4 + 4.0 * M0))
 
-    # ---- ground truth (exact kernel, parity-checked against DuckDB's folds) and ef selection -------------------
+    # ---- ground truth: exact kernel per shard (parity-checked against DuckDB's folds), merged over the shards ------------
     truth = torch.empty((nq, k), dtype=torch.int64, device=dev)
     tdist = torch.empty((nq, k), dtype=torch.float32, device=dev)
     kdev = torch.from_numpy(keys_np).to(dev)
     t_exact = None
     for _ in range(2):  # second call: pools and modules warm
         t0 = time.perf_counter()
-        gvi.exact_topk_device("l2sq", base.data_ptr(), n, q.data_ptr(), nq, d, k, truth.data_ptr(), tdist.data_ptr(), kdev.data_ptr(), stream)
+        gvi.exact_topk_device(metric, base.data_ptr(), n, q.data_ptr(), nq, d, k, truth.data_ptr(), tdist.data_ptr(), kdev.data_ptr(), stream)
         torch.cuda.synchronize()
         t_exact = time.perf_counter() - t0
-    truth_np = truth.cpu().numpy()
+    truth_np = truth.cpu().numpy()            # this shard's exact top-k
+    gtruth_np = truth_np                      # exact top-k over the union of all shards
+    if world > 1:
+        gk = torch.empty((world * nq, k), dtype=torch.int64, device=dev)   # rank-major [world][nq][k]
+        gd = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
+        dist.all_gather_into_tensor(gk, truth)
+        dist.all_gather_into_tensor(gd, tdist)
+        gtruth = torch.empty_like(truth)
+        gtd = torch.empty_like(tdist)
+        gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, gtruth.data_ptr(), gtd.data_ptr(), stream)
+        torch.cuda.synchronize()
+        gtruth_np = gtruth.cpu().numpy()
 
     okeys = torch.empty((nq, k), dtype=torch.int64, device=dev)
     odist = torch.empty((nq, k), dtype=torch.float32, device=dev)
     ocnt = torch.empty(nq, dtype=torch.int32, device=dev)
     ostat = torch.zeros((nq, 4), dtype=torch.int32, device=dev)
+    mk = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    md = torch.empty((nq, k), dtype=torch.float32, device=dev)
 
-    def search(ef, stats=False):
-        ix.search_device(q.data_ptr(), nq, k, ef, okeys.data_ptr(), odist.data_ptr(), ocnt.data_ptr(),
+    def search(ef, stats=False, qptr=None):
+        ix.search_device(qptr or q.data_ptr(), nq, k, ef, okeys.data_ptr(), odist.data_ptr(), ocnt.data_ptr(),
                          ostat.data_ptr() if stats else 0, stream)
 
-    sweep = {}
+    def nccl_merge(out_k, out_d):
+        dist.all_gather_into_tensor(gk, okeys)
+        dist.all_gather_into_tensor(gd, odist)
+        gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, out_k.data_ptr(), out_d.data_ptr(), stream)
+
+    # ---- operating point: smallest ef of the sweep whose recall@10 (of the merged list, N > 1) is >= 0.95 ---------------
+    sweep, shard_sweep = {}, {}
     ef = args.ef
     for e in ([args.ef] if args.ef else EF_SWEEP):
         search(e)
+        if world > 1:
+            nccl_merge(mk, md)
         torch.cuda.synchronize()
-        r = synth.recall_at_k(okeys.cpu().numpy(), truth_np)
+        shard_sweep[e] = round(synth.recall_at_k(okeys.cpu().numpy(), truth_np), 4)
+        r = synth.recall_at_k(mk.cpu().numpy(), gtruth_np) if world > 1 else shard_sweep[e]
         sweep[e] = round(r, 4)
         ef = e
         if r >= 0.95:
             break
-    recall_min = None
+    recall = sweep[ef]                         # N > 1: merged list vs exact top-k over the union (identical on every rank)
+    recall_min = recall_max = shard_sweep[ef]
     if world > 1:
-        # weak scaling: every shard runs at the operating point of shard 0 (the N=1 workload), so the work per GPU does not
-        # change with N; the smallest recall any shard reaches at that ef is reported next to shard 0's
-        te = torch.tensor([ef], dtype=torch.int64, device=dev)
-        dist.broadcast(te, src=0)
-        if int(te.item()) != ef:
-            ef = int(te.item())
-            search(ef)
-            torch.cuda.synchronize()
-            sweep[ef] = round(synth.recall_at_k(okeys.cpu().numpy(), truth_np), 4)
-        tr = torch.tensor([sweep[ef]], dtype=torch.float64, device=dev)
+        tr = torch.tensor([shard_sweep[ef], -shard_sweep[ef]], dtype=torch.float64, device=dev)
         dist.all_reduce(tr, op=dist.ReduceOp.MIN)
-        recall_min = float(tr.item())
-    recall = sweep[ef]
+        recall_min, recall_max = float(tr[0].item()), -float(tr[1].item())
     search(ef, stats=True)
     torch.cuda.synchronize()
     st = ostat.cpu().numpy().view(np.uint32)
     algo_bytes = algorithmic_bytes(st, d, M, M0, k)
+    ref_keys_np = okeys.cpu().numpy()
 
-    # multi-GPU exchange of the per-shard lists (12*nq*k bytes per rank) + device merge. Preferred: the merge kernel reads the
-    # peers' lists over NVLink out of symmetric memory and the ranks synchronise through flags in peer memory (no collective
-    # per step); fallback (GVSS_EXCHANGE=nccl, or symmetric memory unavailable): NCCL all-gather + merge of the gathered copy.
+    # ---- multi-GPU exchange of the per-shard lists (12*nq*k bytes per rank) + device merge ------------------------------
+    # Preferred: the merge kernel reads the peers' lists over NVLink out of symmetric memory and the ranks synchronise through
+    # flags in peer memory (no collective per step); fallback (GVSS_EXCHANGE=nccl, or symmetric memory unavailable): NCCL
+    # all-gather + merge of the gathered copy. The merge runs on its own stream behind an event: step s+1's search does not
+    # wait for step s's exchange (two result-buffer sets alternate).
     exchange, peer = "none", None
+    s_merge = torch.cuda.Stream(dev) if world > 1 else None
     if world > 1:
-        mk = torch.empty((nq, k), dtype=torch.int64, device=dev)
-        md = torch.empty((nq, k), dtype=torch.float32, device=dev)
         want_p2p = os.environ.get("GVSS_EXCHANGE", "p2p") != "nccl"
         ok = torch.zeros(1, dtype=torch.int32, device=dev)
         if want_p2p:
@@ -325,86 +386,111 @@ def main():
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)  # all ranks or none
         if int(ok.item()) == 0:
             peer = None
-        exchange = "nvlink peer reads + flags in peer memory (k_merge_peers)" if peer else "nccl all_gather + k_merge"
+        exchange = ("nvlink peer reads + flags in peer memory (k_merge_peers) on a second stream" if peer
+                    else "nccl all_gather + k_merge")
+    searched = [torch.cuda.Event() for _ in range(2)]      # search of buffer set b has finished
+    merged = [torch.cuda.Event() for _ in range(2)]        # merge that read buffer set b has finished
+    step_no = [0]
+
+    def step(qptr=None):
+        """one step: search (stream A); exchange + merge (stream B behind an event). Returns nothing; results in mk/md."""
         if not peer:
-            gk = torch.empty((world * nq, k), dtype=torch.int64, device=dev)   # rank-major [world][nq][k]
-            gd = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
-
-    def search_step():
-        if peer:
-            kp, dp = peer.outputs()
-            ix.search_device(q.data_ptr(), nq, k, ef, kp, dp, ocnt.data_ptr(), 0, stream)
-        else:
-            search(ef)
-
-    def exchange_step():
-        if peer:
+            search(ef, qptr=qptr)
+            if world > 1:
+                nccl_merge(mk, md)
+            return
+        b = step_no[0] & 1
+        step_no[0] += 1
+        s_search.wait_event(merged[b])                  # the merge two steps ago has released this buffer set
+        kp, dp = peer.outputs()
+        ix.search_device(qptr or q.data_ptr(), nq, k, ef, kp, dp, ocnt.data_ptr(), 0, stream)
+        searched[b].record(s_search)
+        with torch.cuda.stream(s_merge):
+            s_merge.wait_event(searched[b])
             peer.merge(mk, md)
-        elif world > 1:
-            dist.all_gather_into_tensor(gk, okeys)
-            dist.all_gather_into_tensor(gd, odist)
-            gv.merge_topk_device(gk.data_ptr(), gd.data_ptr(), world, nq, k, mk.data_ptr(), md.data_ptr(), stream)
+            merged[b].record(s_merge)
 
-    def step():
-        search_step()
-        exchange_step()
+    def drain():
+        if s_merge is not None:
+            s_merge.synchronize()
+        torch.cuda.synchronize()
 
     for _ in range(args.warmup):
         step()
-    torch.cuda.synchronize()
+    drain()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     l0 = gv.lib().gvss_kernel_launches()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-          for _ in range(args.steps)]
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
         t_wall0 = time.perf_counter()
-        for a, b, c in ev:
-            a.record()
-            search_step()
-            b.record()
-            exchange_step()
-            c.record()
-        torch.cuda.synchronize()
+        t_begin.record(s_search)
+        for a, b in ev:
+            a.record(s_search)
+            step()
+            b.record(s_search)                           # end of this step's search launch (the merge is on the other stream)
+        (s_merge or s_search).wait_stream(s_search)
+        t_end.record(s_merge or s_search)                # after the last merge AND the last search
+        drain()
         t_wall = time.perf_counter() - t_wall0
     launches = gv.lib().gvss_kernel_launches() - l0
-    t_dev = sum(a.elapsed_time(c) for a, b, c in ev) / 1e3           # whole steps, device time
-    t_kernel = sum(a.elapsed_time(b) for a, b, c in ev) / 1e3 / args.steps  # search launch alone (roofline)
+    t_dev = t_begin.elapsed_time(t_end) / 1e3                                # whole timed region, device time
+    t_kernel = sum(a.elapsed_time(b) for a, b in ev) / 1e3 / args.steps      # search launch alone (roofline)
+    per_rank_kernel_ms = [1e3 * t_kernel]
     if world > 1:
         tt = torch.tensor([t_dev], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_dev = float(tt.item())
+        tk = torch.zeros(world, dtype=torch.float64, device=dev)
+        tk[rank] = 1e3 * t_kernel
+        dist.all_reduce(tk)
+        per_rank_kernel_ms = [round(float(v), 3) for v in tk.tolist()]
         dist.barrier()
-    merged_recall = None
+
+    # ---- N > 1 checks: peer-memory exchange == NCCL exchange; merged recall after the timed loop ------------------------
+    exchange_check, global_recall_after = None, None
     if world > 1:
-        # the merged list must contain this shard's own best hits wherever they beat the other shards'; and, when the
-        # peer-memory exchange is active, equal the result of the NCCL all-gather + merge path on the same inputs
-        merged_recall = "n/a (per-shard ground truth only)"
+        step()
+        drain()
+        global_recall_after = synth.recall_at_k(mk.cpu().numpy(), gtruth_np)
         if peer:
-            search_step()
-            exchange_step()
             search(ef)
-            gk2 = torch.empty((world * nq, k), dtype=torch.int64, device=dev)
-            gd2 = torch.empty((world * nq, k), dtype=torch.float32, device=dev)
-            dist.all_gather_into_tensor(gk2, okeys)
-            dist.all_gather_into_tensor(gd2, odist)
             mk2, md2 = torch.empty_like(mk), torch.empty_like(md)
-            gv.merge_topk_device(gk2.data_ptr(), gd2.data_ptr(), world, nq, k, mk2.data_ptr(), md2.data_ptr(), stream)
+            nccl_merge(mk2, md2)
             torch.cuda.synchronize()
             same = torch.tensor([int(torch.equal(mk, mk2) and torch.equal(md, md2))], dtype=torch.int32, device=dev)
             dist.all_reduce(same, op=dist.ReduceOp.MIN)
-            merged_recall = "peer-memory merge == nccl all_gather merge on all ranks" if int(same.item()) else "MISMATCH between peer-memory and nccl merge"
+            exchange_check = "peer-memory merge == nccl all_gather merge on all ranks" if int(same.item()) else "MISMATCH between peer-memory and nccl merge"
+            late = ctypes.c_uint32(0)
+            gv.capi.check(gv.lib().gvss_peer_exchange_status(ctypes.byref(late)))
+            if late.value:
+                exchange_check = f"TIMEOUT waiting for ranks (bit mask {late.value:#x})"
 
-    # ---- e2e through the host-pointer C-ABI call (pinned host buffers; H2D + kernel + D2H inside the timed region) --
+    # ---- e2e from HOST buffers: H2D of the queries + search (+ exchange + merge) + D2H of the result list, every step ----
     qh = torch.from_numpy(q_np).pin_memory()
     kh = torch.empty((nq, k), dtype=torch.int64).pin_memory()
     dh = torch.empty((nq, k), dtype=torch.float32).pin_memory()
     ch = torch.empty(nq, dtype=torch.int32).pin_memory()
+    q_in = torch.empty_like(q)
 
-    def e2e_step():
-        gv.capi.check(gv.lib().gvss_search(ix._h, ctypes.c_void_p(qh.data_ptr()), nq, k, ef, ctypes.c_void_p(kh.data_ptr()),
-                                           ctypes.c_void_p(dh.data_ptr()), ctypes.c_void_p(ch.data_ptr()), None))
+    if world == 1:
+        def e2e_step():  # the public host-pointer call
+            gv.capi.check(gv.lib().gvss_search(ix._h, ctypes.c_void_p(qh.data_ptr()), nq, k, ef, ctypes.c_void_p(kh.data_ptr()),
+                                               ctypes.c_void_p(dh.data_ptr()), ctypes.c_void_p(ch.data_ptr()), None))
+        e2e_api = "gvss_search (host pointers)"
+        h2d, d2h = nq * d * 4, nq * k * 12 + nq * 4 + 256
+    else:
+        def e2e_step():  # host queries -> this rank's GPU -> shard search -> exchange + merge -> merged list back on the host
+            q_in.copy_(qh, non_blocking=True)
+            step(qptr=q_in.data_ptr())
+            with torch.cuda.stream(s_merge):
+                kh.copy_(mk, non_blocking=True)
+                dh.copy_(md, non_blocking=True)
+            drain()
+        e2e_api = "pinned host queries -> gvss_search_device per shard -> gvss_merge_topk_peers_device -> merged list to pinned host"
+        h2d, d2h = nq * d * 4, nq * k * 12
     for _ in range(3):
         e2e_step()
     if world > 1:
@@ -417,14 +503,12 @@ def main():
         tt = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         t_e2e = float(tt.item())
-    e2e_recall = synth.recall_at_k(kh.numpy(), truth_np)
-    h2d = nq * d * 4
-    d2h = nq * k * 12 + nq * 4 + nq * 16
+    e2e_recall = synth.recall_at_k(kh.numpy(), gtruth_np)
 
     # bulk build end to end: rows in (pageable) host memory -> gvss_add_batch -> gvss_flush (staging copy + H2D + graph build)
     build_e2e = None
-    if world == 1:
-        iy = gv.Index(d, "l2sq", M=M, M0=M0, ef_construction=EFC_BENCH, ef_search=64, device=local)
+    if world == 1 and not strong:
+        iy = gv.Index(d, metric, M=M, M0=M0, ef_construction=EFC_BENCH, ef_search=64, device=local)
         iy.reserve(n, 1)
         t0 = time.perf_counter()
         iy.add_batch(base_np, keys=keys_np)
@@ -439,42 +523,51 @@ def main():
     if world > 1:
         tt = torch.tensor([t_build], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        build_vps = world * n / float(tt.item())
+        build_vps = n_total / float(tt.item())
 
+    failed = world > 1 and exchange_check is not None and not exchange_check.startswith("peer-memory merge ==")
     if rank == 0:
         peak, peak_src = peaks()
         achieved = algo_bytes / t_kernel / 1e9
         traffic = None  # dram read+write bytes of one launch from the committed ncu --set full capture of this exact config
-        try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "r2_search_traffic.json")))
-            c = tj["config"]
-            if (c["n"], c["nq"], c["ef_search"], c["M"], c["dims"]) == (n, nq, ef, M, d):
-                traffic = tj["traffic_bytes_per_launch"]
-        except Exception:
-            traffic = None
+        for name in ("r3_search_traffic.json", "r2_search_traffic.json"):
+            try:
+                tj = json.load(open(os.path.join(ROOT, "profiles", name)))
+                c = tj["config"]
+                if (c["n"], c["nq"], c["ef_search"], c["M"], c["dims"]) == (n, nq, ef, M, d) and tj.get("kernel_version", "r2") == gv.lib().gvss_version().decode().split()[1]:
+                    traffic = tj["traffic_bytes_per_launch"]
+                    break
+            except Exception:
+                continue
         cpu = None
         if world == 1 and not args.no_cpu:
-            cpu = cpu_baseline(args, ix.save, q_np, ef, truth_np, gpu_keys=kh.numpy())
-        units = world * nq * args.steps
+            cpu = cpu_baseline(args, d, metric, ix.save, q_np, ef, truth_np, gpu_keys=ref_keys_np)
+        units = (nq if strong else world * nq) * args.steps
         line = {
             "metric": METRIC, "value": units / t_dev, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
+            "scaling": "strong" if strong else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "1M x FLOAT[128] l2sq (SIFT-1M shape) per GPU, 10k-query batch, k=10",
-                       "generator": "clustered(C=N/100, r=16) seed 42 (SURVEY.md App. D law, numpy)", "n_per_gpu": n,
+            "config": {"workload": label, "generator": gen, "n_per_gpu": n, "n_total": n_total,
                        "queries_per_step": nq, "k": k, "ef_search": ef, "recall_at_10": recall, "ef_sweep": sweep,
                        "M": M, "M0": M0, "ef_construction": EFC_BENCH,
-                       "units": "per-shard query searches summed over ranks (every query visits every shard)",
+                       "units": ("queries answered by the whole job (each query is searched on every shard of the one partitioned set)" if strong
+                                 else "per-shard query searches summed over ranks (every query visits every shard)"),
                        "global_queries_per_s": nq * args.steps / t_dev,
-                       "l2_policy": "inputs larger than L2: 512 MB vectors + 128 MB adjacency per GPU vs 126 MB L2; no flush",
+                       "global_recall_at_10": recall if world > 1 else None,
+                       "global_recall_at_10_after_timed_loop": global_recall_after,
+                       "recall_definition": ("merged top-10 vs exact top-10 over the union of all shards" if world > 1
+                                             else "top-10 vs exact top-10 (gvss_exact_topk, bit-exact vs DuckDB's folds)"),
+                       "shard_recall_at_10_min_max": [recall_min, recall_max], "shard_ef_sweep_rank0": shard_sweep,
+                       "l2_policy": f"inputs larger than L2: {n * d * 4 / 1e6:.0f} MB vectors + {n * M0 * 4 / 1e6:.0f} MB adjacency per GPU vs 126 MB L2; no flush",
                        "parallelism": f"shard{world}" if world > 1 else "single", "exchange": exchange,
-                       "exchange_check": merged_recall, "recall_at_10_min_over_shards": recall_min},
+                       "exchange_check": exchange_check, "per_rank_kernel_ms": per_rank_kernel_ms},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "kernel": "k_search<l2sq>",
+                         "traffic": traffic, "peak_source": peak_src, "kernel": f"k_search<{metric}>",
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": 1e3 * t_kernel},
             "cpu_baseline": cpu,
-            "e2e": {"value": world * nq * args.steps / t_e2e, "unit": "queries/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "recall_at_10": e2e_recall, "api": "gvss_search (host pointers)"},
+            "e2e": {"value": units / t_e2e, "unit": "queries/s", "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "recall_at_10": e2e_recall, "api": e2e_api},
             "gpu_launches": int(launches),
             "clocks": clocks.summary(),
             "build": {"value": build_vps, "unit": "vectors/s", "seconds": t_build, "kernel_launches": int(build_launches),
@@ -485,11 +578,12 @@ def main():
                                      "rows_written": bst["rows_written"] / max(1, bst["inserts"])},
                       "e2e": build_e2e,
                       "roofline": {"bound": "hbm", "achieved": build_bytes / t_build / 1e9, "peak": peak, "unit": "GB/s",
-                                   "frac": build_bytes / t_build / 1e9 / peak, "kernel": "k_build<l2sq>",
-                                   "algorithmic_bytes": build_bytes, "note": "wall clock of the whole bulk build incl. uploads and the 16 ramp launches"}},
+                                   "frac": build_bytes / t_build / 1e9 / peak, "kernel": f"k_build<{metric}>",
+                                   "algorithmic_bytes": build_bytes, "note": "wall clock of the whole bulk build incl. uploads and the ramp launches"}},
             "exact_topk": {"seconds": t_exact, "queries": nq, "base": n, "queries_per_s": nq / t_exact,
                            "roofline": {"bound": "tensor", "achieved": 6.0 * nq * n * d / t_exact / 1e12, "peak": tensor_peak_tf32()[0],
                                         "unit": "TFLOP/s", "frac": 6.0 * nq * n * d / t_exact / 1e12 / tensor_peak_tf32()[0],
+                                        "fp32_accurate_tflops": 2.0 * nq * n * d / t_exact / 1e12,
                                         "peak_source": tensor_peak_tf32()[1],
                                         "note": "3xTF32: 3 tensor passes x 2*Q*N*d flops over the wall clock of the whole call (split, tiles, merge, re-rank)"},
                            "note": "ground truth: tcgen05 3xTF32 candidate tiles + exact re-rank (bit-exact vs DuckDB folds), 2nd call, wall clock incl. plane split"},
@@ -498,6 +592,8 @@ def main():
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+    if failed:
+        raise SystemExit(3)
 
 
 if __name__ == "__main__":
