@@ -44,6 +44,7 @@ READ_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t)
 # every symbol include/gvss.h declares (tests/test_abi.py checks the header against this table)
 SIGNATURES = {
     "gvss_create": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p)]),
+    "gvss_create_sharded": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_int32), C.c_uint32, C.POINTER(C.c_void_p)]),
     "gvss_destroy": (None, [C.c_void_p]),
     "gvss_reset": (C.c_int, [C.c_void_p]),
     "gvss_reserve": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32]),

@@ -509,7 +509,9 @@ __device__ __forceinline__ unsigned long long global_ns() {
 __global__ void k_merge_peers(PeerLists pl, uint32_t rank, uint32_t shards, uint32_t step, uint64_t nq, uint32_t k,
                               int64_t *__restrict__ keys_out, float *__restrict__ dist_out, unsigned long long timeout_ns) {
     const uint32_t lane = threadIdx.x & 31u;
-    if (blockIdx.x == 0 && threadIdx.x < shards) {
+    // step == 0: one process drives all GPUs and has ordered this launch behind the shards' searches with CUDA events
+    // (router.cu): no handshake, the lists are simply read where they are
+    if (step && blockIdx.x == 0 && threadIdx.x < shards) {
         __threadfence_system();
         st_release_sys(pl.flags[threadIdx.x] + rank, step);
     }
@@ -517,7 +519,7 @@ __global__ void k_merge_peers(PeerLists pl, uint32_t rank, uint32_t shards, uint
     // of this very grid: waiting on it would make every CTA depend on CTA 0 having been scheduled, which CUDA does not
     // promise once the grid exceeds what the GPU holds at once.
     bool late = false;
-    if (lane < shards && lane != rank) {
+    if (step && lane < shards && lane != rank) {
         const uint32_t *mine = pl.flags[rank] + lane;
         const unsigned long long t0 = global_ns();
         while ((int32_t)(ld_acquire_sys(mine) - step) < 0) { // wrap-safe "reached step"
@@ -580,7 +582,7 @@ cudaError_t launch_merge_topk_peers(const int64_t *const *peer_keys, const float
     for (uint32_t s = 0; s < shards; s++) {
         pl.keys[s] = reinterpret_cast<const unsigned long long *>(peer_keys[s]);
         pl.dist[s] = peer_dist[s];
-        pl.flags[s] = peer_flags[s];
+        pl.flags[s] = peer_flags ? peer_flags[s] : nullptr;
     }
     const uint32_t wpb = 4;
     const unsigned grid = (unsigned)(((nq ? nq : 1) + wpb - 1) / wpb); // at least CTA 0: the flags must be published even for an empty batch

@@ -3,6 +3,7 @@
 // HNSWIndex::index (reference src/include/hnsw/hnsw_index.hpp:28,39). No CPU fallback: every compute entry
 // point needs a CUDA device and fails loudly without one.
 #include "kernels.h"
+#include "router.h"
 
 #include <algorithm>
 #include <atomic>
@@ -28,6 +29,15 @@ void count_launch(uint64_t n) { g_launches += n; }
 
 static thread_local std::string t_error;
 static int fail(const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    t_error = buf;
+    return 1;
+}
+int set_error(const char *fmt, ...) { // for router.cu
     char buf[512];
     va_list ap;
     va_start(ap, fmt);
@@ -130,6 +140,8 @@ struct gvss_index {
     std::condition_variable slot_cv;
     std::vector<std::unique_ptr<SearchSlot>> slots;
     uint32_t slots_peak = 0; // most slots busy at the same time
+
+    Router *router = nullptr; // gvss_create_sharded: this handle only routes to one single-GPU index per device (router.cu)
 };
 
 namespace gvss {
@@ -481,8 +493,22 @@ int gvss_create(const gvss_config *config, gvss_index **out) {
     API_END
 }
 
+int gvss_create_sharded(const gvss_config *config, const int32_t *devices, uint32_t n_devices, gvss_index **out) {
+    API_BEGIN
+    if (!config || !devices || !out) return fail("gvss_create_sharded: null argument");
+    Router *r = nullptr;
+    if (router_create(config, devices, n_devices, &r)) return 1;
+    auto *x = new gvss_index();
+    x->cfg = *config;
+    x->router = r;
+    *out = x;
+    return 0;
+    API_END
+}
+
 void gvss_destroy(gvss_index *x) {
     if (!x) return;
+    if (x->router) { router_destroy(x->router); delete x; return; }
     cudaSetDevice(x->device);
     wait_device_searches(x);
     free_device(x);
@@ -507,6 +533,7 @@ static void reset_locked(gvss_index *x) {
 int gvss_reset(gvss_index *x) {
     API_BEGIN
     if (!x) return fail("null index");
+    if (x->router) return router_reset(x->router);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     reset_locked(x);
@@ -526,6 +553,7 @@ __global__ void k_pack_rows(const float *__restrict__ vectors, uint32_t dpad, ui
 int gvss_compact_rebuild(gvss_index *x, uint64_t *dropped) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return router_compact(x->router, true, dropped);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     if (flush_locked(x)) return 1;
@@ -575,6 +603,7 @@ int gvss_compact_rebuild(gvss_index *x, uint64_t *dropped) {
 int gvss_reserve(gvss_index *x, uint64_t members, uint32_t host_threads) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return router_reserve(x->router, members, host_threads);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     if (host_threads == 0) host_threads = 1;
@@ -596,6 +625,7 @@ int gvss_reserve(gvss_index *x, uint64_t members, uint32_t host_threads) {
 int gvss_add(gvss_index *x, int64_t key, const float *vec, uint32_t host_thread) {
     API_BEGIN
     if (!x || !vec) return fail("gvss_add: null argument");
+    if (x->router) return router_add(x->router, key, vec, host_thread);
     if (!x->poisoned.empty()) return check_usable(x);
     size_t t;
     if (host_thread == GVSS_ANY_THREAD) t = x->stages.size() - 1;
@@ -619,6 +649,7 @@ int gvss_add_batch(gvss_index *x, const int64_t *keys, const float *vecs, uint64
     API_BEGIN
     if (!x || (!vecs && n)) return fail("gvss_add_batch: null argument");
     if (check_usable(x)) return 1;
+    if (x->router) return router_add_batch(x->router, keys, vecs, n);
     std::shared_lock<std::shared_mutex> lk(x->rw); // a flush may not run between the capacity test and the append
     if (x->room.fetch_sub((int64_t)n) < (int64_t)n) {
         x->room.fetch_add((int64_t)n);
@@ -638,6 +669,7 @@ int gvss_add_batch_device(gvss_index *x, const int64_t *keys_host, const float *
     API_BEGIN
     if (!x || (!vecs_device && n)) return fail("gvss_add_batch_device: null argument");
     if (check_usable(x)) return 1;
+    if (x->router) return fail("gvss_add_batch_device: not available on a sharded index (the rows live on one GPU): pass host rows to gvss_add_batch");
     std::unique_lock<std::shared_mutex> lk(x->rw);
     if (x->room.fetch_sub((int64_t)n) < (int64_t)n) {
         x->room.fetch_add((int64_t)n);
@@ -655,6 +687,7 @@ int gvss_add_batch_device(gvss_index *x, const int64_t *keys_host, const float *
 int gvss_flush(gvss_index *x) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return router_flush(x->router);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     return flush_locked(x);
@@ -664,6 +697,7 @@ int gvss_flush(gvss_index *x) {
 int gvss_set_build_concurrency(gvss_index *x, uint32_t n) {
     API_BEGIN
     if (!x) return fail("null index");
+    if (x->router) return router_set_build_concurrency(x->router, n);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     x->build_conc = n;
     return 0;
@@ -673,6 +707,7 @@ int gvss_set_build_concurrency(gvss_index *x, uint32_t n) {
 int gvss_remove(gvss_index *x, int64_t key, uint64_t *removed) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return router_remove(x->router, key, removed);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     if (flush_locked(x)) return 1;
@@ -706,6 +741,7 @@ int gvss_remove(gvss_index *x, int64_t key, uint64_t *removed) {
 int gvss_compact(gvss_index *x) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return router_compact(x->router, false, nullptr);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     if (flush_locked(x)) return 1;
@@ -718,6 +754,7 @@ int gvss_search_device(gvss_index *x, const float *queries, uint64_t nq, uint32_
                        float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out, void *cuda_stream) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return fail("gvss_search_device: not available on a sharded index (one device pointer cannot name every GPU): use gvss_search");
     if (nq && (!queries || !keys_out)) return fail("gvss_search_device: null buffer");
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
@@ -732,6 +769,7 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
                                float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out, void *cuda_stream) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (x->router) return fail("gvss_search_device_noalloc: not available on a sharded index");
     if (nq && (!queries || !keys_out)) return fail("gvss_search_device_noalloc: null buffer");
     std::shared_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
@@ -751,54 +789,87 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     API_END
 }
 
-// Host-pointer search. Calls from different host threads run concurrently: each takes a slot (stream + scratch + I/O
-// buffers) and holds rw only shared. One H2D copy (queries), one launch, one D2H copy (work words | counts | keys |
-// distances [| stats], packed) per call.
+} // extern "C"
+namespace gvss {
+// Host-pointer search, first half: takes a slot of `x` (stream + scratch + I/O buffers), uploads the queries and launches
+// k_search on the slot's stream. Results stay in the slot's device buffer: [work words | counts | keys | distances | stats].
+// The caller holds x->rw shared until host_search_release.
+int host_search_launch(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, uint32_t ef, bool want_stats, HostSearch &hs) {
+    hs = HostSearch{};
+    hs.x = x;
+    cudaSetDevice(x->device);
+    if (flush_if_staged(x)) return 1;
+    hs.lock = std::shared_lock<std::shared_mutex>(x->rw);
+    SearchSlot *s = acquire_slot(x);
+    if (!s) return 1;
+    hs.slot = s;
+    hs.stream = s->stream;
+    const uint32_t d = x->cfg.dimensions;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    hs.q_bytes = up(nq * d * 4ull);
+    hs.o_counts = 256; hs.o_keys = hs.o_counts + up(nq * 4); hs.o_dist = hs.o_keys + up(nq * k * 8ull);
+    hs.o_stats = hs.o_dist + up(nq * k * 4ull);
+    hs.r_bytes = hs.o_stats + (want_stats ? up(nq * sizeof(gvss_search_stats)) : 0);
+    if (ensure_bytes(s->d_io, s->io_bytes, hs.q_bytes + hs.r_bytes)) return 1;
+    if (hs.r_bytes > s->h_io_bytes) {
+        if (s->h_io) cudaFreeHost(s->h_io);
+        s->h_io = nullptr; s->h_io_bytes = 0;
+        CU(cudaMallocHost(&s->h_io, hs.r_bytes));
+        s->h_io_bytes = hs.r_bytes;
+    }
+    hs.res = s->d_io + hs.q_bytes;
+    hs.h_res = s->h_io;
+    hs.d_keys = reinterpret_cast<int64_t *>(hs.res + hs.o_keys);
+    hs.d_dist = reinterpret_cast<float *>(hs.res + hs.o_dist);
+    SearchParams p;
+    uint32_t grid = 0;
+    if (plan_search(x, reinterpret_cast<const float *>(s->d_io), nq, k, ef, hs.d_keys, hs.d_dist,
+                    reinterpret_cast<uint32_t *>(hs.res + hs.o_counts),
+                    want_stats ? reinterpret_cast<gvss_search_stats *>(hs.res + hs.o_stats) : nullptr, p, grid)) return 1;
+    if (ensure_bytes(s->d_scratch, s->scratch_bytes, p.sl.bytes_per_warp * grid)) return 1;
+    p.scratch = s->d_scratch;
+    p.work_counter = reinterpret_cast<unsigned long long *>(hs.res);
+    p.fail_word = p.work_counter + 1;
+    CU(cudaMemcpyAsync(s->d_io, queries, nq * d * 4ull, cudaMemcpyHostToDevice, s->stream));
+    CU(cudaMemsetAsync(hs.res, 0, 16, s->stream));
+    CU(launch_search(metric_id(x->cfg.metric), view_of(x), p, grid, s->stream));
+    return 0;
+}
+// second half: everything packed comes back in ONE copy; returns 1 + the index of a query that overflowed in *failed
+int host_search_fetch(HostSearch &hs, unsigned long long *failed) {
+    cudaSetDevice(hs.x->device);
+    CU(cudaMemcpyAsync(hs.h_res, hs.res, hs.r_bytes, cudaMemcpyDeviceToHost, hs.stream));
+    CU(cudaStreamSynchronize(hs.stream));
+    *failed = reinterpret_cast<const unsigned long long *>(hs.h_res)[1];
+    return 0;
+}
+void host_search_release(HostSearch &hs) {
+    if (hs.slot) release_slot(hs.x, hs.slot);
+    hs.slot = nullptr;
+    if (hs.lock.owns_lock()) hs.lock.unlock();
+}
+
+} // namespace gvss
+extern "C" {
+// Calls from different host threads run concurrently: each takes a slot and holds rw only shared. One H2D copy (queries),
+// one launch, one D2H copy per call.
 int gvss_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, uint32_t ef, int64_t *keys_out,
                 float *dist_out, uint32_t *counts_out, gvss_search_stats *stats_out) {
     API_BEGIN
     if (check_usable(x)) return 1;
     if (nq && (!queries || (!keys_out && k))) return fail("gvss_search: null buffer");
-    cudaSetDevice(x->device);
-    if (flush_if_staged(x)) return 1;
-    if (!nq) return 0;
-    if (!k) { if (counts_out) memset(counts_out, 0, nq * 4); return 0; }
-    std::shared_lock<std::shared_mutex> lk(x->rw);
-    SearchSlot *s = acquire_slot(x);
-    if (!s) return 1;
-    SlotGuard guard{x, s};
-    const uint32_t d = x->cfg.dimensions;
-    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
-    const size_t q_bytes = up(nq * d * 4ull);
-    const size_t o_work = 0, o_counts = 256, o_keys = o_counts + up(nq * 4), o_dist = o_keys + up(nq * k * 8ull),
-                 o_stats = o_dist + up(nq * k * 4ull), r_bytes = o_stats + (stats_out ? up(nq * sizeof(gvss_search_stats)) : 0);
-    if (ensure_bytes(s->d_io, s->io_bytes, q_bytes + r_bytes)) return 1;
-    if (r_bytes > s->h_io_bytes) {
-        if (s->h_io) cudaFreeHost(s->h_io);
-        s->h_io = nullptr; s->h_io_bytes = 0;
-        CU(cudaMallocHost(&s->h_io, r_bytes));
-        s->h_io_bytes = r_bytes;
-    }
-    uint8_t *res = s->d_io + q_bytes;
-    SearchParams p;
-    uint32_t grid = 0;
-    if (plan_search(x, reinterpret_cast<const float *>(s->d_io), nq, k, ef, reinterpret_cast<int64_t *>(res + o_keys),
-                    reinterpret_cast<float *>(res + o_dist), reinterpret_cast<uint32_t *>(res + o_counts),
-                    stats_out ? reinterpret_cast<gvss_search_stats *>(res + o_stats) : nullptr, p, grid)) return 1;
-    if (ensure_bytes(s->d_scratch, s->scratch_bytes, p.sl.bytes_per_warp * grid)) return 1;
-    p.scratch = s->d_scratch;
-    p.work_counter = reinterpret_cast<unsigned long long *>(res + o_work);
-    p.fail_word = p.work_counter + 1;
-    CU(cudaMemcpyAsync(s->d_io, queries, nq * d * 4ull, cudaMemcpyHostToDevice, s->stream));
-    CU(cudaMemsetAsync(res + o_work, 0, 16, s->stream));
-    CU(launch_search(metric_id(x->cfg.metric), view_of(x), p, grid, s->stream));
-    CU(cudaMemcpyAsync(s->h_io, res, r_bytes, cudaMemcpyDeviceToHost, s->stream));
-    CU(cudaStreamSynchronize(s->stream));
-    const unsigned long long failed = reinterpret_cast<const unsigned long long *>(s->h_io + o_work)[1];
-    memcpy(keys_out, s->h_io + o_keys, nq * k * 8ull);
-    if (dist_out) memcpy(dist_out, s->h_io + o_dist, nq * k * 4ull);
-    if (counts_out) memcpy(counts_out, s->h_io + o_counts, nq * 4);
-    if (stats_out) memcpy(stats_out, s->h_io + o_stats, nq * sizeof(gvss_search_stats));
+    if (x->router) return router_search(x->router, queries, nq, k, ef, keys_out, dist_out, counts_out, stats_out);
+    if (!nq) return flush_if_staged(x);
+    if (!k) { if (counts_out) memset(counts_out, 0, nq * 4); return flush_if_staged(x); }
+    HostSearch hs;
+    struct Rel { HostSearch &h; ~Rel() { host_search_release(h); } } rel{hs};
+    if (host_search_launch(x, queries, nq, k, ef, stats_out != nullptr, hs)) return 1;
+    unsigned long long failed = 0;
+    if (host_search_fetch(hs, &failed)) return 1;
+    memcpy(keys_out, hs.h_res + hs.o_keys, nq * k * 8ull);
+    if (dist_out) memcpy(dist_out, hs.h_res + hs.o_dist, nq * k * 4ull);
+    if (counts_out) memcpy(counts_out, hs.h_res + hs.o_counts, nq * 4);
+    if (stats_out) memcpy(stats_out, hs.h_res + hs.o_stats, nq * sizeof(gvss_search_stats));
     // a query whose candidate queue ran out of room was cut short: the synchronous path cannot return it
     if (failed) return fail("gvss_search: candidate queue overflow on query %llu (beam %u)", failed - 1, std::max(ef ? ef : 64u, k));
     return 0;
@@ -809,6 +880,7 @@ int gvss_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, ui
 int gvss_serialized_length(gvss_index *x, uint64_t *bytes) {
     API_BEGIN
     if (check_usable(x) || !bytes) return x && bytes ? 1 : fail("null argument");
+    if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
     std::shared_lock<std::shared_mutex> lk(x->rw);
@@ -824,6 +896,7 @@ int gvss_save(gvss_index *x, int (*write)(void *, const void *, size_t), void *u
     API_BEGIN
     if (!x || !write) return fail("gvss_save: null argument");
     if (check_usable(x)) return 1;
+    if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
     std::shared_lock<std::shared_mutex> lk(x->rw);
@@ -998,6 +1071,7 @@ static int load_into(gvss_index *y, int (*read)(void *, void *, size_t), void *u
 int gvss_load(gvss_index *x, int (*read)(void *, void *, size_t), void *user) {
     API_BEGIN
     if (!x || !read) return fail("gvss_load: null argument");
+    if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     // parsed and uploaded into an index of its own, which changes places with this one only when the whole stream was good
@@ -1022,6 +1096,7 @@ int gvss_load(gvss_index *x, int (*read)(void *, void *, size_t), void *user) {
 int gvss_get_info(gvss_index *x, gvss_info *out) {
     API_BEGIN
     if (!x || !out) return fail("null argument");
+    if (x->router) return router_info(x->router, out);
     std::shared_lock<std::shared_mutex> lk(x->rw);
     memset(out, 0, sizeof *out);
     const uint64_t staged = x->staged.load();
@@ -1048,6 +1123,7 @@ int gvss_get_build_stats(gvss_index *x, gvss_build_stats *out) {
     API_BEGIN
     if (!x || !out) return fail("null argument");
     if (check_usable(x)) return 1;
+    if (x->router) return router_build_stats(x->router, out);
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
     std::shared_lock<std::shared_mutex> lk(x->rw);
@@ -1063,6 +1139,7 @@ int gvss_get_level_stats(gvss_index *x, uint32_t level, gvss_level_stats *out) {
     API_BEGIN
     if (!x || !out) return fail("null argument");
     if (check_usable(x)) return 1;
+    if (x->router) return router_level_stats(x->router, level, out);
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
     std::shared_lock<std::shared_mutex> lk(x->rw);

@@ -17,11 +17,16 @@ def _ptr(a):
 class Index:
     """``index_dense_gt<row_t>::make(metric, config)`` (hnsw_index.cpp:162-189) on a B200."""
 
-    def __init__(self, dims, metric="l2sq", M=0, M0=0, ef_construction=0, ef_search=0, device=-1):
+    def __init__(self, dims, metric="l2sq", M=0, M0=0, ef_construction=0, ef_search=0, device=-1, devices=None):
+        """``devices=[0, 1, ...]``: one logical index partitioned over those GPUs (``gvss_create_sharded``)."""
         self._h = C.c_void_p()
         cfg = capi.Config(int(dims), METRIC_CHAR[metric], int(M), int(M0), int(ef_construction), int(ef_search),
                           int(device))
-        capi.check(capi.lib().gvss_create(C.byref(cfg), C.byref(self._h)))
+        if devices is None:
+            capi.check(capi.lib().gvss_create(C.byref(cfg), C.byref(self._h)))
+        else:
+            arr = (C.c_int32 * len(devices))(*[int(v) for v in devices])
+            capi.check(capi.lib().gvss_create_sharded(C.byref(cfg), arr, len(devices), C.byref(self._h)))
         self.dims = int(dims)
 
     def close(self):

@@ -16,6 +16,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <string>
@@ -160,8 +161,20 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         c.expansion_add = (uint32_t)config.expansion_add;
         c.expansion_search = (uint32_t)config.expansion_search;
         c.device = -1;
-        if (metric.scalar_kind() != scalar_kind_t::f32_k) r.create_error_ = "only f32 vectors are supported";
-        else if (gvss_create(&c, &r.handle_)) { r.create_error_ = last_error(); r.handle_ = nullptr; }
+        if (metric.scalar_kind() != scalar_kind_t::f32_k) { r.create_error_ = "only f32 vectors are supported"; return r; }
+        // GVSS_DEVICES=0,1,2,3: partition every index over those GPUs (gvss_create_sharded). In-memory databases only: a
+        // sharded index is not one usearch stream, so PersistToDisk fails with the library's message.
+        std::vector<int32_t> devices;
+        if (const char *e = std::getenv("GVSS_DEVICES"))
+            for (const char *p = e; *p;) {
+                char *end = nullptr;
+                const long v = std::strtol(p, &end, 10);
+                if (end == p) break;
+                devices.push_back((int32_t)v);
+                p = *end == ',' ? end + 1 : end;
+            }
+        const int rc = devices.size() > 1 ? gvss_create_sharded(&c, devices.data(), (uint32_t)devices.size(), &r.handle_) : gvss_create(&c, &r.handle_);
+        if (rc) { r.create_error_ = last_error(); r.handle_ = nullptr; }
         return r;
     }
     explicit operator bool() const noexcept { return handle_ != nullptr; }

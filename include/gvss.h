@@ -84,6 +84,16 @@ typedef struct gvss_search_stats {
 /* --- lifetime ----------------------------------------------------------------------------------------------- */
 /* index_dense_gt<row_t>::make(metric, config), hnsw_index.cpp:162-189 */
 int gvss_create(const gvss_config *config, gvss_index **out);
+/* One logical index partitioned over several GPUs of this process (no counterpart in the reference, which is
+ * single-process CPU code): one sub-graph per device, rows dealt out in chunks of 2048 in arrival order, keys stay the
+ * caller's global row ids, no build-time communication. Every other entry point takes the handle unchanged: gvss_add* route
+ * rows, gvss_flush builds all shards at the same time, gvss_search uploads the batch to every GPU, searches all shards
+ * concurrently and merges the per-shard lists by (distance, key) in one kernel on devices[0] that reads the other GPUs' lists
+ * over NVLink (peer access; a staged copy without it). devices: n_devices CUDA ordinals (1..16, repeats allowed);
+ * shards * k <= 256 per search; searches on one sharded handle are serialised. NOT available on a sharded handle:
+ * gvss_save / gvss_load / gvss_serialized_length (a sharded index is not one usearch stream — the reference cannot merge
+ * indexes either, hnsw_index.cpp:561-563 — so persisted indexes stay single-GPU), gvss_search_device*, gvss_add_batch_device. */
+int gvss_create_sharded(const gvss_config *config, const int32_t *devices, uint32_t n_devices, gvss_index **out);
 void gvss_destroy(gvss_index *index);
 /* index.reset(), hnsw_index.cpp:384 */
 int gvss_reset(gvss_index *index);

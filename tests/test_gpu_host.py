@@ -191,3 +191,82 @@ def test_flush_that_cannot_allocate_keeps_the_rows_and_the_index():
         ix.reserve(2 ** 31 - 100, 1)       # beyond the addressable slots (and beyond any HBM)
     np.testing.assert_array_equal(ix.ef_search(q, 5, 32)[0], want)
     assert ix.capacity() == 2000
+
+
+def _host_merge(parts, k):
+    """(keys, dist) per shard -> merged top-k by (distance, key), the order k_merge / k_merge_peers define"""
+    keys = np.concatenate([p[0] for p in parts], axis=1)
+    dist = np.concatenate([p[1] for p in parts], axis=1)
+    out_k = np.empty((keys.shape[0], k), np.int64)
+    out_d = np.empty((keys.shape[0], k), np.float32)
+    for i in range(keys.shape[0]):
+        valid = keys[i] >= 0
+        order = np.lexsort((keys[i][valid], dist[i][valid]))[:k]
+        out_k[i], out_d[i] = -1, np.inf
+        out_k[i, :len(order)] = keys[i][valid][order]
+        out_d[i, :len(order)] = dist[i][valid][order]
+    return out_k, out_d
+
+
+def test_sharded_handle_equals_separate_indexes_plus_merge():
+    """gvss_create_sharded (here: three shards on ONE GPU, which exercises all of the routing): rows are dealt out in chunks of
+    2048, every shard is searched, lists are merged by (distance, key). The same thing done by hand with three plain indexes
+    gives identical ids and distance bits; counts, size, removal and the refusals behave as documented."""
+    n, d, k, ef, G = 9000, 24, 10, 96, 3
+    base, q = synth.clustered(n, d, 90, 6, 21, 150)
+    keys = np.arange(n, dtype=np.int64) + 10_000
+    ix = gv.Index(d, "l2sq", M=16, devices=[0] * G)
+    ix.reserve(n, 1)
+    ix.set_build_concurrency(1)          # sequential builds are deterministic: the hand-made copy below gets the same graphs
+    ix.add_batch(base, keys=keys)
+    ix.flush()
+    info = ix.info()
+    assert info["size"] == n and info["node_count"] == n and info["capacity"] == n
+    got_k, got_d, got_c, st = ix.ef_search(q, k, ef, stats=True)
+    parts = []
+    for s in range(G):
+        rows = np.concatenate([np.arange(c, min(n, c + 2048)) for c in range(s * 2048, n, G * 2048)])
+        iy = gv.Index(d, "l2sq", M=16)
+        iy.reserve(len(rows) + 2048, 1)
+        iy.set_build_concurrency(1)
+        iy.add_batch(base[rows], keys=keys[rows])
+        iy.flush()
+        parts.append(iy.ef_search(q, k, ef, stats=True))
+    want_k, want_d = _host_merge(parts, k)
+    np.testing.assert_array_equal(got_k, want_k)
+    np.testing.assert_array_equal(got_d.view(np.uint32), want_d.view(np.uint32))
+    assert (got_c == k).all()
+    np.testing.assert_array_equal(st["computed"], sum(p[3]["computed"] for p in parts))
+    truth, _ = gv.exact_topk("l2sq", base, q, k, keys=keys)
+    assert synth.recall_at_k(got_k, truth) > 0.97
+    # removal reaches whichever shard holds the row
+    victim = int(got_k[0, 0])
+    assert ix.remove(victim) == 1 and ix.size() == n - 1
+    assert victim not in ix.ef_search(q[:1], k, ef)[0]
+    with pytest.raises(gv.GvssError, match="not one usearch stream"):
+        ix.save()
+    with pytest.raises(gv.GvssError, match="Reserve capacity"):
+        ix.add_batch(base[:5], keys=np.arange(5))     # n - 1 live rows + 5 > capacity n
+
+
+def test_sharded_handle_takes_adds_from_host_threads():
+    """T construct tasks call add(key, vec, thread) on a sharded handle exactly as on a plain one."""
+    n, d, T = 5000, 8, 4
+    base, q = synth.clustered(n, d, 40, 4, 23, 0)
+    ix = gv.Index(d, "l2sq", devices=[0, 0])
+    ix.reserve(n, T)
+    errs = []
+
+    def work(t):
+        try:
+            for i in range(t, n, T):
+                ix.add(i, base[i], thread=t)
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+    ts = [threading.Thread(target=work, args=(t,)) for t in range(T)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    assert ix.size() == n
+    keys, dist, _ = ix.ef_search(base[:500], 1, 64)
+    assert (dist[:, 0] == 0).all() and list(keys[:, 0]) == list(range(500))
