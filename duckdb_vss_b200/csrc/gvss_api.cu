@@ -19,6 +19,7 @@
 #include <deque>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -140,6 +141,14 @@ struct gvss_index {
     std::condition_variable slot_cv;
     std::vector<std::unique_ptr<SearchSlot>> slots;
     uint32_t slots_peak = 0; // most slots busy at the same time
+
+    // background build (gvss_set_background_build): a library-owned thread inserts staged rows while the caller adds more
+    std::thread bg;
+    std::mutex bg_mu;
+    std::condition_variable bg_cv;
+    bool bg_stop = false;
+    std::atomic<uint64_t> bg_min_rows{0};
+    std::string bg_error; // first failure of a background flush (guarded by bg_mu), reported by the next gvss_flush
 
     Router *router = nullptr; // gvss_create_sharded: this handle only routes to one single-GPU index per device (router.cu)
 };
@@ -437,6 +446,42 @@ static void clear_staging(gvss_index *x) {
     x->staged = 0;
 }
 
+// the body of the background builder. It sleeps until `bg_min_rows` rows are staged, then takes the writer lock
+// and inserts whatever is staged at that moment — upload and graph construction overlap the caller's table scan. Adding
+// never waits for it (gvss_add only touches its staging buffer); searches wait for the chunk in flight like for any flush.
+static void background_builder(gvss_index *x) {
+    cudaSetDevice(x->device);
+    for (;;) {
+        {
+            std::unique_lock<std::mutex> lk(x->bg_mu);
+            x->bg_cv.wait(lk, [&] { return x->bg_stop || (x->bg_min_rows.load() && x->staged.load() >= x->bg_min_rows.load()); });
+            if (x->bg_stop) return;
+        }
+        std::unique_lock<std::shared_mutex> lk(x->rw);
+        if (!x->poisoned.empty()) { x->bg_min_rows = 0; continue; } // nothing more to do for a broken index: go back to sleep
+        if (!x->bg_min_rows.load() || x->staged.load() < x->bg_min_rows.load()) continue;
+        if (flush_locked(x)) {
+            std::lock_guard<std::mutex> el(x->bg_mu);
+            if (x->bg_error.empty()) x->bg_error = t_error;
+            x->bg_min_rows = 0; // stop trying; the foreground flush reports the error
+        }
+    }
+}
+static void stop_background_builder(gvss_index *x) {
+    if (!x->bg.joinable()) return;
+    {
+        std::lock_guard<std::mutex> lk(x->bg_mu);
+        x->bg_stop = true;
+    }
+    x->bg_cv.notify_all();
+    x->bg.join();
+    x->bg_stop = false;
+}
+static inline void poke_background_builder(gvss_index *x) {
+    const uint64_t m = x->bg_min_rows.load(std::memory_order_relaxed);
+    if (m && x->staged.load(std::memory_order_relaxed) >= m) x->bg_cv.notify_one();
+}
+
 } // namespace gvss
 
 // every ABI body runs inside this pair: nothing may throw across the C boundary (std::bad_alloc, std::length_error ...)
@@ -509,6 +554,7 @@ int gvss_create_sharded(const gvss_config *config, const int32_t *devices, uint3
 void gvss_destroy(gvss_index *x) {
     if (!x) return;
     if (x->router) { router_destroy(x->router); delete x; return; }
+    stop_background_builder(x);
     cudaSetDevice(x->device);
     wait_device_searches(x);
     free_device(x);
@@ -641,6 +687,7 @@ int gvss_add(gvss_index *x, int64_t key, const float *vec, uint32_t host_thread)
     st.vecs.insert(st.vecs.end(), vec, vec + x->cfg.dimensions);
     st.keys.push_back(key);
     x->staged.fetch_add(1); // inside the lock: whoever takes the row away has seen it counted
+    poke_background_builder(x);
     return 0;
     API_END
 }
@@ -650,17 +697,22 @@ int gvss_add_batch(gvss_index *x, const int64_t *keys, const float *vecs, uint64
     if (!x || (!vecs && n)) return fail("gvss_add_batch: null argument");
     if (check_usable(x)) return 1;
     if (x->router) return router_add_batch(x->router, keys, vecs, n);
-    std::shared_lock<std::shared_mutex> lk(x->rw); // a flush may not run between the capacity test and the append
+    // default keys number the rows in arrival order: no flush may run between reading the node count and the append
+    std::shared_lock<std::shared_mutex> lk(x->rw, std::defer_lock);
+    if (!keys) lk.lock();
     if (x->room.fetch_sub((int64_t)n) < (int64_t)n) {
         x->room.fetch_add((int64_t)n);
         return fail("Reserve capacity ahead of insertions!");
     }
     gvss_index::Stage &st = *x->stages.front(); // same buffer as thread 0: call order is insertion order
-    std::lock_guard<std::mutex> sl(st.mu);
-    st.vecs.insert(st.vecs.end(), vecs, vecs + n * x->cfg.dimensions);
-    const int64_t first = (int64_t)(x->count + x->staged.load());
-    for (uint64_t i = 0; i < n; i++) st.keys.push_back(keys ? keys[i] : first + (int64_t)i);
-    x->staged += n;
+    {
+        std::lock_guard<std::mutex> sl(st.mu);
+        st.vecs.insert(st.vecs.end(), vecs, vecs + n * x->cfg.dimensions);
+        const int64_t first = keys ? 0 : (int64_t)(x->count + x->staged.load());
+        for (uint64_t i = 0; i < n; i++) st.keys.push_back(keys ? keys[i] : first + (int64_t)i);
+        x->staged += n;
+    }
+    poke_background_builder(x);
     return 0;
     API_END
 }
@@ -688,9 +740,29 @@ int gvss_flush(gvss_index *x) {
     API_BEGIN
     if (check_usable(x)) return 1;
     if (x->router) return router_flush(x->router);
+    {
+        std::lock_guard<std::mutex> el(x->bg_mu);
+        if (!x->bg_error.empty()) {
+            const std::string why = x->bg_error;
+            x->bg_error.clear();
+            return fail("background build failed: %s", why.c_str());
+        }
+    }
     std::unique_lock<std::shared_mutex> lk(x->rw);
     cudaSetDevice(x->device);
     return flush_locked(x);
+    API_END
+}
+
+int gvss_set_background_build(gvss_index *x, uint64_t min_rows) {
+    API_BEGIN
+    if (check_usable(x)) return 1;
+    if (x->router) return router_set_background_build(x->router, min_rows);
+    x->bg_min_rows = min_rows;
+    if (min_rows && !x->bg.joinable()) x->bg = std::thread(background_builder, x);
+    if (!min_rows) stop_background_builder(x);
+    else poke_background_builder(x);
+    return 0;
     API_END
 }
 

@@ -369,9 +369,13 @@ struct LeftSrc {
 // Distances from one left-hand vector to up to 32 rows: lane i (if `active`) gets d(left, vectors[my_slot]).
 // `staged` remembers which row sits in stage[0][lane] so that back-to-back calls over the same rows
 // (neighbour-selection steps) do not touch HBM/L2 again when a row is a single chunk.
-template <int METRIC>
+// MODE = 1: the production search configuration is fixed at compile time — query-to-node distances through gather4
+// staging, whole-row and visited-window prefetches on, list-as-queue allowed — so none of the alternative paths (kept for
+// A/B measurements and for the build) takes part in k_search's register allocation. MODE = 0: configuration from WarpWs.
+template <int METRIC, int MODE = 0>
 __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, LeftSrc left, uint32_t my_slot,
                                                 bool active, uint32_t &staged) {
+    if (MODE == 1) return warp_distances_g4<METRIC>(g, w, my_slot, active);
     const uint32_t lane = lane_id();
     const uint32_t chunk = w.chunk;
     const uint32_t nchunks = (g.dpad + chunk - 1) / chunk;
@@ -686,12 +690,12 @@ __device__ __forceinline__ uint32_t *list_ptr(const GraphView &g, uint32_t slot,
 }
 
 // search_for_one_ (index.hpp:3384-3422): greedy descent from `closest` through levels begin..end+1.
-template <int METRIC, bool VOLATILE>
+template <int METRIC, bool VOLATILE, int MODE = 0>
 __device__ __forceinline__ uint32_t greedy_descent(const GraphView &g, WarpWs &w, uint32_t closest, int begin_level,
                                                    int end_level, Counters &cnt, uint32_t &staged) {
     const uint32_t lane = lane_id();
     LeftSrc q{w.q, 0};
-    float cd = warp_distances<METRIC>(g, w, q, closest, lane == 0, staged);
+    float cd = warp_distances<METRIC, MODE>(g, w, q, closest, lane == 0, staged);
     cd = __shfl_sync(kFull, cd, 0);
     cnt.computed++;
     for (int level = begin_level; level > end_level; --level) {
@@ -707,7 +711,7 @@ __device__ __forceinline__ uint32_t greedy_descent(const GraphView &g, WarpWs &w
                 const uint32_t vmask = __ballot_sync(kFull, valid);
                 if (!vmask) break;
                 cnt.computed += __popc(vmask);
-                const float d = warp_distances<METRIC>(g, w, q, s, valid, staged);
+                const float d = warp_distances<METRIC, MODE>(g, w, q, s, valid, staged);
                 // sequential scan with a running minimum == first strict minimum in list order
                 float best = valid ? d : CUDART_INF_F;
                 uint32_t bl = lane;
@@ -772,11 +776,13 @@ __device__ __forceinline__ uint32_t top_upper_bound(const float *td, uint32_t n,
 constexpr uint32_t kExpanded = 0x80000000u;
 constexpr uint32_t kSlotMask = 0x7FFFFFFFu;
 
-template <int METRIC, bool INSERT, bool VOLATILE>
+template <int METRIC, bool INSERT, bool VOLATILE, int MODE = 0>
 __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, uint32_t limit, int level,
                                             uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged, bool lq = false) {
     const uint32_t lane = lane_id();
     const uint32_t lt_mask = (1u << lane) - 1u;
+    const bool cfg_g4 = MODE == 1 ? true : w.g4, cfg_pf_rows = MODE == 1 ? true : w.prefetch_rows,
+               cfg_pf_vis = MODE == 1 ? true : w.prefetch_vis, cfg_spec = MODE == 1 ? false : w.spec_prefetch;
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
     uint32_t scan_from = 0; // LQ: every list entry before this index is expanded
@@ -813,7 +819,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     top_size = 0;
     vis_clear(w);
 
-    float radius = warp_distances<METRIC>(g, w, q, start, lane == 0, staged);
+    float radius = warp_distances<METRIC, MODE>(g, w, q, start, lane == 0, staged);
     radius = __shfl_sync(kFull, radius, 0);
     if (radius != radius) radius = CUDART_INF_F;
     cnt.computed++;
@@ -930,7 +936,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         uint32_t cap;
         const uint32_t *list = list_ptr(g, c.s, level, cap);
         uint32_t nnew = 0;
-        if (w.prefetch_vis && !w.use_bitmap && cap > 32) {
+        if (cfg_pf_vis && !w.use_bitmap && cap > 32) {
             // the visited windows of the second block of neighbours start their trip from DRAM while the first block is tested
             const uint32_t s1 = 32 + lane < cap ? ld_adj<VOLATILE>(list + 32 + lane) : kInvalid;
             if (s1 != kInvalid) prefetch_l2(w.vis + (((s1 * 2654435761u) >> 7) & w.vis_mask & ~(kVisWindow - 1)));
@@ -942,7 +948,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             OPCLK(t_v0);
             if (base == 0) OPC(kOpClkAdj, t_v0 - t_gather);
             const bool valid = s != kInvalid && s < g.count;
-            if (w.spec_prefetch && valid) { // start pulling the row towards L2 while the visited test is in flight
+            if (cfg_spec && valid) { // start pulling the row towards L2 while the visited test is in flight
                 const float *row = g.vectors + (size_t)s * g.dpad;
                 for (uint32_t l = 0; l * 32 < g.dpad; l++) prefetch_l2(row + l * 32);
             }
@@ -968,15 +974,15 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         // the likely next candidate's list has reached L2 by now: read it, and after the distance phase start the visited
         // windows of ITS neighbours on their way from DRAM (a hint only: wrong guesses cost 32 bytes of traffic each)
         uint32_t sp0 = kInvalid, sp1 = kInvalid;
-        if (w.prefetch_vis && !w.use_bitmap && plist) {
+        if (cfg_pf_vis && !w.use_bitmap && plist) {
             if (lane < pcap) sp0 = ld_adj<VOLATILE>(plist + lane);
             if (32 + lane < pcap) sp1 = ld_adj<VOLATILE>(plist + 32 + lane);
         }
         OPCLK(t_dist);
         OPC(kOpClkGather, t_dist - t_gather);
         // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
-        const uint32_t bw = ((GVSS_DIRECT_PATH && w.direct) || w.g4) ? 32u : w.stage_rows; // rows per distance batch
-        if (w.g4 && w.prefetch_rows) {
+        const uint32_t bw = ((GVSS_DIRECT_PATH && MODE == 0 && w.direct) || cfg_g4) ? 32u : w.stage_rows; // rows per distance batch
+        if (cfg_g4 && cfg_pf_rows) {
             // gather4 staging takes one 128-byte line of every row per step: get ALL lines of all new rows moving towards L2
             // now, so that only the first step of the hop waits for DRAM
             const uint32_t lines = (g.dpad * 4 + 127) / 128;
@@ -993,7 +999,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         for (uint32_t b = 0; b < nnew; b += bw) {
             const bool act = lane < bw && b + lane < nnew;
             const uint32_t s = act ? w.nb[b + lane] : kInvalid;
-            const float d = warp_distances<METRIC>(g, w, q, s, act, staged);
+            const float d = warp_distances<METRIC, MODE>(g, w, q, s, act, staged);
             // a NaN distance (NULL / NaN query rows reach the index join, hnsw_lateral_join.test:57-67) is ordered as +inf:
             // the reference only guarantees termination there, and a total order keeps the merge below well defined
             if (act) w.nd[b + lane] = (d == d) ? d : CUDART_INF_F;

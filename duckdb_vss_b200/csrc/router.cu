@@ -163,6 +163,11 @@ int router_set_build_concurrency(Router *r, uint32_t n) {
     return 0;
 }
 
+int router_set_background_build(Router *r, uint64_t min_rows) {
+    for (auto *s : r->shards) if (gvss_set_background_build(s, min_rows)) return 1;
+    return 0;
+}
+
 int router_remove(Router *r, int64_t key, uint64_t *removed) {
     uint64_t total = 0;
     for (auto *s : r->shards) { // keys are global: whichever shard holds the row removes it

@@ -38,6 +38,7 @@ int router_add(Router *r, int64_t key, const float *vec, uint32_t host_thread);
 int router_add_batch(Router *r, const int64_t *keys, const float *vecs, uint64_t n);
 int router_flush(Router *r);
 int router_set_build_concurrency(Router *r, uint32_t n);
+int router_set_background_build(Router *r, uint64_t min_rows);
 int router_remove(Router *r, int64_t key, uint64_t *removed);
 int router_compact(Router *r, bool rebuild, uint64_t *dropped);
 int router_search(Router *r, const float *queries, uint64_t nq, uint32_t k, uint32_t ef, int64_t *keys_out, float *dist_out,

@@ -52,7 +52,8 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
 #ifndef GVSS_SEARCH_MIN_BLOCKS
 #define GVSS_SEARCH_MIN_BLOCKS 24
 #endif
-template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOCKS) k_search(GraphView g, const __grid_constant__ SearchParams p) {
+// MODE: see warp_distances (hnsw_device.cuh). launch_search picks MODE 1 whenever the run-time configuration is the default one.
+template <int METRIC, int MODE> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOCKS) k_search(GraphView g, const __grid_constant__ SearchParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     WarpWs w;
     carve(w, smem, p.sm, p.scratch, p.sl, p.direct, &p.vmap);
@@ -68,7 +69,7 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         const float *qsrc = p.queries + qi * (p.query_stride ? p.query_stride : g.dims);
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = i < g.dims ? __ldg(qsrc + i) : 0.0f;
         __syncwarp();
-        if (METRIC == kCos && w.g4) w.q_a2 = fold_a2(w.q, g.dpad);
+        if (METRIC == kCos && (MODE == 1 || w.g4)) w.q_a2 = fold_a2(w.q, g.dpad);
 
         Counters cnt = {0, 0, 0, (long long)qi == p.trace_query ? 0x80000000u : 0u};
         uint32_t top_size = 0;
@@ -77,24 +78,24 @@ template <int METRIC> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOC
         for (int i = 0; i < kOpCount; i++) w.opc[i] = i == kOpQueries ? 1ull : 0ull;
 #endif
         if (p.cluster_out) { // compact (index.hpp:3043-3046): only the node the descent through levels max_level..1 ends at
-            const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            const uint32_t closest = greedy_descent<METRIC, false, MODE>(g, w, p.entry, p.max_level, 0, cnt, staged);
             if (lane == 0) p.cluster_out[qi] = closest;
             __syncwarp();
             continue;
         }
         if (g.count && p.k) {
-            const uint32_t closest = greedy_descent<METRIC, false>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            const uint32_t closest = greedy_descent<METRIC, false, MODE>(g, w, p.entry, p.max_level, 0, cnt, staged);
             const Counters before = cnt;
             // list-as-queue first (hashed visited table); a query that would overfill the table is redone with the exact
             // bitmap (flag bit1); exact ties switch to usearch's heap mid-flight (flag bit2), or — if the operation log ran
             // out of room — repeat the query with the heap from the start
-            const bool lq_ok = (p.direct & 8) == 0;
+            const bool lq_ok = MODE == 1 || (p.direct & 8) == 0;
             bool lq = lq_ok, bitmap = false;
             OPCLK(t_q0);
             for (;;) {
                 cnt = before;
                 w.use_bitmap = bitmap;
-                beam_search<METRIC, false, false>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged, lq);
+                beam_search<METRIC, false, false, MODE>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged, lq);
                 if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
                 if (cnt.flags & 8u) { lq = false; continue; }
                 break;
@@ -212,12 +213,17 @@ uint32_t resident_warps(int device, uint32_t smem_bytes, bool build) {
 
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st);
 
-template <int METRIC> static cudaError_t launch_search_t(const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(k_search<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
+template <int METRIC, int MODE> static cudaError_t launch_search_tm(const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(k_search<METRIC, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
     if (e != cudaSuccess) return e;
-    k_search<METRIC><<<grid, 32, p.sm.bytes, st>>>(g, p);
+    k_search<METRIC, MODE><<<grid, 32, p.sm.bytes, st>>>(g, p);
     count_launch();
     return cudaGetLastError();
+}
+template <int METRIC> static cudaError_t launch_search_t(const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
+    // p.direct == 16: gather4 staging and nothing else switched away from its default (GVSS_SEARCH_GENERIC=1 forces MODE 0)
+    static const bool generic = [] { const char *e = getenv("GVSS_SEARCH_GENERIC"); return e && atoi(e); }();
+    return (p.direct == 16 && !generic) ? launch_search_tm<METRIC, 1>(g, p, grid, st) : launch_search_tm<METRIC, 0>(g, p, grid, st);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

@@ -61,6 +61,10 @@ class Index:
     def set_build_concurrency(self, n):
         capi.check(capi.lib().gvss_set_build_concurrency(self._h, int(n)))
 
+    def set_background_build(self, min_rows):
+        """Rows staged by add() are inserted by a library thread as soon as ``min_rows`` wait (0 = off)."""
+        capi.check(capi.lib().gvss_set_background_build(self._h, int(min_rows)))
+
     def remove(self, key):
         n = C.c_uint64()
         capi.check(capi.lib().gvss_remove(self._h, int(key), C.byref(n)))

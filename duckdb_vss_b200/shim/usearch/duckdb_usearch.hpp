@@ -174,7 +174,12 @@ template <typename key_at = std::int64_t> class index_dense_gt {
                 p = *end == ',' ? end + 1 : end;
             }
         const int rc = devices.size() > 1 ? gvss_create_sharded(&c, devices.data(), (uint32_t)devices.size(), &r.handle_) : gvss_create(&c, &r.handle_);
-        if (rc) { r.create_error_ = last_error(); r.handle_ = nullptr; }
+        if (rc) { r.create_error_ = last_error(); r.handle_ = nullptr; return r; }
+        // pipelined bulk load: rows are uploaded and inserted in the background as soon as this many are staged,
+        // while the construct tasks (or, with n3_streaming_sink.patch, the Sink phase) keep adding. GVSS_BACKGROUND_BUILD=0: off
+        unsigned long long bg = 32768;
+        if (const char *e = std::getenv("GVSS_BACKGROUND_BUILD")) bg = std::strtoull(e, nullptr, 10);
+        if (bg) gvss_set_background_build(r.handle_, bg);
         return r;
     }
     explicit operator bool() const noexcept { return handle_ != nullptr; }

@@ -121,6 +121,13 @@ int gvss_flush(gvss_index *index);
  * plays in index.reserve({members, threads}) (hnsw_index_physical_create.cpp:296; index_limits_t, index.hpp:1134-1140):
  * with 1 the build is sequential and reproduces the reference's single-thread graph byte for byte. */
 int gvss_set_build_concurrency(gvss_index *index, uint32_t max_concurrent_inserts);
+/* Pipelined bulk load (the reference collects every row first and builds after Finalize,
+ * hnsw_index_physical_create.cpp:98-128,283-306): with min_rows > 0 a library-owned thread uploads and inserts the staged
+ * rows whenever at least min_rows of them wait, while the caller goes on adding — table scan, H2D and graph construction
+ * overlap, and gvss_flush only drains the rest. 0 switches it off (default). Row order within one staging buffer is kept,
+ * so a single adder with gvss_set_build_concurrency(1) still gets the reference's sequential graph. A failure of a
+ * background insert is reported by the next gvss_flush. */
+int gvss_set_background_build(gvss_index *index, uint64_t min_rows);
 /* index.remove(key), hnsw_index.cpp:478: lazy delete (index_dense.hpp:1228-1255); unknown key: *removed = 0. */
 int gvss_remove(gvss_index *index, int64_t key, uint64_t *removed);
 /* index.compact(), hnsw_index.cpp:458 = index_gt::compact (index.hpp:3007-3096): re-orders the nodes by (level descending,
