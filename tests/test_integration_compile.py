@@ -1,0 +1,58 @@
+"""CPU: the drop-in claim at compile level. The reference's UNCHANGED extension sources must compile against the gvss shim
+(duckdb_vss_b200/shim ahead of the vendored usearch on the include path), and the two optional operator patches
+(integration/n1_batched_index_join.patch, integration/n3_streaming_sink.patch) must apply to the reference and compile.
+Needs the reference checkout (/root/reference): skipped where it is absent (the GPU box). The linked and SQL-tested
+artefact is integration/build_sql.sh + integration/run_sql_tests.sh (profiles/r3_sql_tests_gpu.log)."""
+import os
+import shutil
+import subprocess
+from concurrent.futures import ThreadPoolExecutor
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get("VSS_REFERENCE_DIR", "/root/reference")
+HNSW = ["hnsw_index.cpp", "hnsw_index_macros.cpp", "hnsw_index_physical_create.cpp", "hnsw_index_pragmas.cpp", "hnsw_index_scan.cpp",
+        "hnsw_index_plan.cpp", "hnsw_topk_operator.cpp", "hnsw_optimize_expr.cpp", "hnsw_optimize_join.cpp", "hnsw_optimize_topk.cpp",
+        "hnsw_optimize_scan.cpp"]
+
+pytestmark = pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src", "hnsw")), reason="reference checkout not present")
+
+
+def _syntax_check(src, extra_includes=()):
+    cmd = ["g++", "-std=c++17", "-fsyntax-only", "-DDUCKDB_USEARCH_USE_SIMSIMD=0", "-w"]
+    for inc in list(extra_includes) + [f"{ROOT}/duckdb_vss_b200/shim", f"{ROOT}/include", f"{REF}/src/include",
+                                      f"{REF}/duckdb/src/include", f"{REF}/duckdb/third_party/re2", f"{REF}/duckdb/third_party/fmt/include",
+                                      f"{REF}/duckdb/extension/core_functions/include"]:
+        cmd += ["-I", inc]
+    r = subprocess.run(cmd + ["-M", src], capture_output=True, text=True)   # which duckdb_usearch.hpp did it resolve?
+    assert r.returncode == 0, f"{src}:\n{r.stderr[-3000:]}"
+    deps = r.stdout
+    if "duckdb_usearch.hpp" in deps:
+        assert f"{ROOT}/duckdb_vss_b200/shim/usearch/duckdb_usearch.hpp" in deps, f"{src} resolved the vendored usearch, not the shim"
+        assert f"{REF}/src/include/usearch/index.hpp" not in deps
+    r = subprocess.run(cmd + [src], capture_output=True, text=True)
+    assert r.returncode == 0, f"{src}:\n{r.stderr[-3000:]}"
+    return src
+
+
+def test_unchanged_extension_sources_compile_against_the_shim():
+    srcs = [f"{REF}/src/hnsw/{f}" for f in HNSW] + [f"{REF}/src/vss_extension.cpp"]
+    with ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
+        done = list(ex.map(_syntax_check, srcs))
+    assert len(done) == len(srcs)
+
+
+@pytest.mark.parametrize("patch,files", [
+    ("n1_batched_index_join.patch", ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
+    ("n3_streaming_sink.patch", ["src/hnsw/hnsw_index_physical_create.cpp"]),
+])
+def test_operator_patches_apply_to_the_reference_and_compile(tmp_path, patch, files):
+    for f in files:
+        os.makedirs(tmp_path / os.path.dirname(f), exist_ok=True)
+        shutil.copy(os.path.join(REF, f), tmp_path / f)
+    r = subprocess.run(["patch", "-p1", "-i", os.path.join(ROOT, "integration", patch)], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    srcs = [str(tmp_path / f) for f in files if f.endswith(".cpp")]
+    with ThreadPoolExecutor(max_workers=4) as ex:
+        list(ex.map(lambda s: _syntax_check(s, extra_includes=[str(tmp_path / "src" / "include")]), srcs))
