@@ -40,3 +40,21 @@ def test_multi_scan_prefetch_serves_the_index_join_from_one_batched_search(tmp_p
     assert "prefetch_ok 1 served 2048/2048 same_ids 1 mismatched_counts 0 foreign 0 other_limit 0 after_reset 0" in out
     m = re.search(r"speedup ([0-9.]+)", out)
     assert m and float(m.group(1)) > 5.0  # one launch + one PCIe round trip instead of 2048
+
+
+def test_background_build_overlaps_the_feeding_threads(tmp_path):
+    """T threads feed 2048-row chunks (PhysicalCreateHNSWIndex pattern) at a throttled 'table scan' rate.
+    With gvss_set_background_build the graph is built while the rows arrive: the streamed run ends soon after the scan,
+    the one-shot run pays scan + build; both graphs answer alike."""
+    exe = str(tmp_path / "sink_driver")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-pthread", f"-I{ROOT}/include", f"{ROOT}/tests/cpp/sink_driver.cpp", f"-L{libdir}",
+                    "-lgvss", f"-Wl,-rpath,{libdir}", "-o", exe], check=True)
+    out = subprocess.run([exe, "200000", "64", "8", "250000"], check=True, capture_output=True, text=True, timeout=600).stdout
+    print(out)
+    m = re.search(r"one_shot_s ([0-9.]+) streamed_s ([0-9.]+) scan_s ([0-9.]+) recall_one_shot ([0-9.]+) recall_streamed ([0-9.]+)", out)
+    assert m, out
+    one_shot, streamed, scan, r1, r2 = map(float, m.groups())
+    assert streamed < one_shot                      # the build overlapped the scan ...
+    assert streamed < scan + 0.6 * (one_shot - scan)  # ... for more than a third of its duration
+    assert abs(r1 - r2) < 0.01 and r2 > 0.9
