@@ -418,6 +418,15 @@ def main():
     for _ in range(args.warmup):
         step()
     drain()
+    # this rank's search launch on its own (no exchange, no waiting for peers): what bounds a step when the shards differ
+    iso = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    search(ef)
+    iso[0].record(s_search)
+    for _ in range(3):
+        search(ef)
+    iso[1].record(s_search)
+    torch.cuda.synchronize()
+    t_kernel_alone = iso[0].elapsed_time(iso[1]) / 3.0
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -439,6 +448,7 @@ def main():
     t_dev = t_begin.elapsed_time(t_end) / 1e3                                # whole timed region, device time
     t_kernel = sum(a.elapsed_time(b) for a, b in ev) / 1e3 / args.steps      # search launch alone (roofline)
     per_rank_kernel_ms = [1e3 * t_kernel]
+    per_rank_alone_ms = [t_kernel_alone]
     if world > 1:
         tt = torch.tensor([t_dev], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -447,6 +457,10 @@ def main():
         tk[rank] = 1e3 * t_kernel
         dist.all_reduce(tk)
         per_rank_kernel_ms = [round(float(v), 3) for v in tk.tolist()]
+        tk.zero_()
+        tk[rank] = t_kernel_alone
+        dist.all_reduce(tk)
+        per_rank_alone_ms = [round(float(v), 3) for v in tk.tolist()]
         dist.barrier()
 
     # ---- N > 1 checks: peer-memory exchange == NCCL exchange; merged recall after the timed loop ------------------------
@@ -561,7 +575,9 @@ def main():
                        "shard_recall_at_10_min_max": [recall_min, recall_max], "shard_ef_sweep_rank0": shard_sweep,
                        "l2_policy": f"inputs larger than L2: {n * d * 4 / 1e6:.0f} MB vectors + {n * M0 * 4 / 1e6:.0f} MB adjacency per GPU vs 126 MB L2; no flush",
                        "parallelism": f"shard{world}" if world > 1 else "single", "exchange": exchange,
-                       "exchange_check": exchange_check, "per_rank_kernel_ms": per_rank_kernel_ms},
+                       "exchange_check": exchange_check, "per_rank_kernel_ms": per_rank_kernel_ms,
+                       "per_rank_kernel_ms_without_exchange": per_rank_alone_ms,
+                       "per_rank_note": "kernel_ms = search launch inside the timed steps (a fast rank also waits there for the buffer set the slowest peer still merges); without_exchange = the same launch timed alone: max over ranks of the latter is what a step costs"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "kernel": f"k_search<{metric}>",
                          "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": 1e3 * t_kernel},

@@ -383,7 +383,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
-    if (w.g4 && !stream_left) return warp_distances_g4<METRIC>(g, w, my_slot, active);
+    if (w.g4 && !stream_left) { staged = kInvalid; return warp_distances_g4<METRIC>(g, w, my_slot, active); } // (the gather4 stage overlays the row stage)
 #if GVSS_DIRECT_PATH
     if (w.direct && !stream_left) { // no staging at all: all 32 lanes at once
         const float d = direct_distance<METRIC>(g.vectors, g.dpad, left.smem, my_slot, active);

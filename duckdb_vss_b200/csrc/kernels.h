@@ -14,11 +14,13 @@ struct SmemLayout {
     uint32_t rstride, stage_rows, chunk, nbuf, heap_smem, top_cap, bytes;
 };
 // stage_rows: 32 or 16; with_left: room for a streamed left-hand row chunk (node-to-node distances, build only);
-// list_cap: longest neighbour list (max(M, M0))
+// list_cap: longest neighbour list (max(M, M0)); g4_alias (build): the whole-row stage is 1024-byte aligned so that its first
+// 4 KB can serve as the gather4 stage of the query-to-node distances
 // chunk: floats of a row staged per step (0 = default min(dpad, 128)); double_buffer: two stage buffers when a row spans
 // several chunks (build), else the chunks are staged one after the other into one buffer (search: half the footprint)
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap, uint32_t chunk = 0, bool double_buffer = true, bool gather4 = false);
+                            bool with_left, uint32_t list_cap, uint32_t chunk = 0, bool double_buffer = true, bool gather4 = false,
+                            bool g4_alias = false);
 // tensor map for the gather4 staging path (exact_tc.cu holds the driver entry point); false when the driver refuses
 bool encode_row_gather_map(CUtensorMap *m, const float *vectors, uint64_t rows, uint32_t dpad);
 uint32_t default_heap_smem(uint32_t beam);
@@ -80,6 +82,7 @@ struct BuildParams {
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;
+    alignas(64) CUtensorMap vmap; // direct bit4: query-to-node distances of the insert-time searches stage rows by TMA gather4 through this map
 };
 cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t stream);
 

@@ -124,7 +124,7 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32, GVSS_SEARC
 }
 
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer, bool gather4) {
+                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer, bool gather4, bool g4_alias) {
     SmemLayout s{};
     if (chunk == 0 || chunk > (uint32_t)kChunk) chunk = (uint32_t)kChunk;
     if (gather4) { chunk = kG4Chunk; stage_rows = 32; double_buffer = false; }
@@ -138,9 +138,10 @@ SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem,
     s.nbuf = two ? 2u : 1u;
     uint32_t off = 0;
     auto take = [&](uint32_t bytes, uint32_t align) { off = (off + align - 1) / align * align; uint32_t o = off; off += bytes; return o; };
-    if (gather4) s.off_stage0 = take(stage_bytes, 1024); // swizzle atoms are 1024-byte aligned: first in the carve-out
+    const bool stage_first = gather4 || g4_alias;
+    if (stage_first) s.off_stage0 = take(stage_bytes < 4096u && g4_alias ? 4096u : stage_bytes, 1024); // swizzle atoms are 1024-byte aligned: first in the carve-out
     s.off_mbar = take(16, 16);
-    if (!gather4) s.off_stage0 = take(stage_bytes, 128);
+    if (!stage_first) s.off_stage0 = take(stage_bytes, 128);
     s.off_stage1 = two ? take(stage_bytes, 128) : s.off_stage0;
     s.off_c = take(with_left ? (two ? 2u : 1u) * kChunk * 4 : 0, 128); // streamed left-hand chunk, double-buffered with the stage
     s.off_q = take(dpad * 4, 16);
