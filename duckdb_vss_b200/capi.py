@@ -71,6 +71,7 @@ SIGNATURES = {
                                   C.c_uint32, C.c_void_p, C.c_void_p]),
     "gvss_exact_topk_device": (C.c_int, [C.c_char, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64,
                                          C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gvss_exact_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gvss_merge_topk_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p,
                                          C.c_void_p, C.c_void_p]),
     "gvss_merge_topk_peers_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,

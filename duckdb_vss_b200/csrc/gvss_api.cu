@@ -948,6 +948,66 @@ int gvss_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, ui
     API_END
 }
 
+// Exact (brute-force) top-k over the rows the index already holds in HBM — no copy of the base set: the comparator of the
+// index join / `ORDER BY array_distance LIMIT k` at SQL level. Rows are zero-padded to `dpad` floats in
+// the index and the queries are padded the same way: a trailing +0 term changes no bit of any of the three folds.
+int gvss_exact_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t k, int64_t *keys_out, float *dist_out, uint32_t *counts_out) {
+    API_BEGIN
+    if (check_usable(x)) return 1;
+    if (nq && (!queries || !keys_out)) return fail("gvss_exact_search: null buffer");
+    if (x->router) return fail("gvss_exact_search: not available on a sharded index");
+    if (!k || k > 1024) return fail("gvss_exact_search: k must be in 1..1024");
+    cudaSetDevice(x->device);
+    if (flush_if_staged(x)) return 1;
+    if (!nq) return 0;
+    std::shared_lock<std::shared_mutex> lk(x->rw);
+    const uint64_t n = x->count, live = n - x->n_deleted;
+    // removed members cannot be masked inside the kernels: ask for enough extra candidates to drop them afterwards
+    const uint64_t kk = std::min<uint64_t>(n, (uint64_t)k + x->n_deleted);
+    if (kk > 1024) return fail("gvss_exact_search: %llu removed members are in the way of an exact top-%u; compact the index first", (unsigned long long)x->n_deleted, k);
+    SearchSlot *s = acquire_slot(x);
+    if (!s) return 1;
+    SlotGuard guard{x, s};
+    const uint32_t d = x->cfg.dimensions, dp = x->dpad;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t q_bytes = up(nq * dp * 4ull), o_keys = q_bytes, o_dist = o_keys + up(nq * std::max<uint64_t>(kk, 1) * 8ull),
+                 total = o_dist + up(nq * std::max<uint64_t>(kk, 1) * 4ull);
+    if (ensure_bytes(s->d_io, s->io_bytes, total)) return 1;
+    if (total > s->h_io_bytes) {
+        if (s->h_io) cudaFreeHost(s->h_io);
+        s->h_io = nullptr; s->h_io_bytes = 0;
+        CU(cudaMallocHost(&s->h_io, total));
+        s->h_io_bytes = total;
+    }
+    for (uint64_t i = 0; i < nq; i++) {
+        if (counts_out) counts_out[i] = 0;
+        for (uint32_t j = 0; j < k; j++) { keys_out[i * k + j] = -1; if (dist_out) dist_out[i * k + j] = INFINITY; }
+    }
+    if (!kk) return 0; // empty index
+    float *hq = reinterpret_cast<float *>(s->h_io);
+    if (dp != d) memset(hq, 0, nq * dp * 4ull);
+    for (uint64_t i = 0; i < nq; i++) memcpy(hq + i * dp, queries + i * d, d * 4ull);
+    CU(cudaMemcpyAsync(s->d_io, hq, nq * dp * 4ull, cudaMemcpyHostToDevice, s->stream));
+    if (gvss_exact_topk_device(x->cfg.metric, x->d_vectors, n, x->d_keys, reinterpret_cast<const float *>(s->d_io), nq, dp, (uint32_t)kk,
+                               reinterpret_cast<int64_t *>(s->d_io + o_keys), reinterpret_cast<float *>(s->d_io + o_dist), s->stream)) return 1;
+    CU(cudaMemcpyAsync(s->h_io + o_keys, s->d_io + o_keys, total - o_keys, cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    const int64_t *hk = reinterpret_cast<const int64_t *>(s->h_io + o_keys);
+    const float *hd = reinterpret_cast<const float *>(s->h_io + o_dist);
+    for (uint64_t i = 0; i < nq; i++) {
+        uint32_t c = 0;
+        for (uint64_t j = 0; j < kk && c < k && c < live; j++) {
+            if (hk[i * kk + j] == GVSS_FREE_KEY || hk[i * kk + j] < 0) continue;
+            keys_out[i * k + c] = hk[i * kk + j];
+            if (dist_out) dist_out[i * k + c] = hd[i * kk + j];
+            c++;
+        }
+        if (counts_out) counts_out[i] = c;
+    }
+    return 0;
+    API_END
+}
+
 // ---- persistence -------------------------------------------------------------------------------------------------
 int gvss_serialized_length(gvss_index *x, uint64_t *bytes) {
     API_BEGIN

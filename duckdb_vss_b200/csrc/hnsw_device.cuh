@@ -383,7 +383,8 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
-    if (w.g4 && !stream_left) { staged = kInvalid; return warp_distances_g4<METRIC>(g, w, my_slot, active); } // (the gather4 stage overlays the row stage)
+    // gather4 staging serves the QUERY-to-node distances only (the build also passes left-hand rows that sit in the row stage)
+    if (w.g4 && left.smem == w.q) { staged = kInvalid; return warp_distances_g4<METRIC>(g, w, my_slot, active); } // (the gather4 stage overlays the row stage)
 #if GVSS_DIRECT_PATH
     if (w.direct && !stream_left) { // no staging at all: all 32 lanes at once
         const float d = direct_distance<METRIC>(g.vectors, g.dpad, left.smem, my_slot, active);

@@ -34,7 +34,11 @@ class Index:
             capi.lib().gvss_destroy(self._h)
             self._h = C.c_void_p()
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # interpreter shutdown: the module globals are already gone
+            pass
 
     # --- construction ---
     def reserve(self, members, threads=1):
@@ -97,6 +101,16 @@ class Index:
             return keys[:, :k], dist[:, :k], counts, {"computed": st[:, 0], "visited": st[:, 1],
                                                       "base_hops": st[:, 2], "flags": st[:, 3]}
         return keys[:, :k], dist[:, :k], counts
+
+    def exact_search(self, queries, k):
+        """Brute-force top-k over the rows the index holds in HBM (``gvss_exact_search``): (keys, DuckDB-fold distances, counts)."""
+        q = np.ascontiguousarray(queries, dtype=np.float32).reshape(-1, self.dims)
+        nq = q.shape[0]
+        keys = np.full((nq, k), -1, dtype=np.int64)
+        dist = np.full((nq, k), np.inf, dtype=np.float32)
+        counts = np.zeros(nq, dtype=np.uint32)
+        capi.check(capi.lib().gvss_exact_search(self._h, _ptr(q), nq, int(k), _ptr(keys), _ptr(dist), _ptr(counts)))
+        return keys, dist, counts
 
     def search_device(self, q_ptr, nq, k, ef, keys_ptr, dist_ptr=0, counts_ptr=0, stats_ptr=0, stream=0):
         capi.check(capi.lib().gvss_search_device(self._h, C.c_void_p(q_ptr), int(nq), int(k), int(ef),

@@ -25,13 +25,16 @@ template <typename index_at> class multi_scan_prefetch_t {
 
     // Search rows [0, count) of the contiguous block `queries` (row stride = dims floats) with one batched call.
     // Returns false (and caches nothing) if the index refuses, e.g. count == 0.
+    // exact = true: brute-force top-k over the index's rows instead of the graph search
     bool prefetch(const index_at &index, const float *queries, std::size_t count, std::size_t dims, std::size_t limit,
-                  std::size_t ef_search) {
+                  std::size_t ef_search, bool exact = false) {
         reset();
         if (!queries || !count || !limit) return false;
         keys_.resize(count * limit);
         counts_.resize(count);
-        if (!index.ef_search_batch(queries, count, limit, ef_search, keys_.data(), nullptr, counts_.data())) {
+        const bool ok = exact ? index.exact_search_batch(queries, count, limit, keys_.data(), nullptr, counts_.data())
+                              : index.ef_search_batch(queries, count, limit, ef_search, keys_.data(), nullptr, counts_.data());
+        if (!ok) {
             reset();
             return false;
         }

@@ -220,6 +220,26 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         return handle_ && !gvss_search(handle_, queries, nq, (uint32_t)wanted, (uint32_t)ef, (int64_t *)keys, distances, counts, nullptr);
     }
 
+    // exact (brute-force) top-k over the rows the index holds in HBM (integration/n2_exact_mode.patch)
+    bool exact_search_batch(const float *queries, std::size_t nq, std::size_t wanted, vector_key_t *keys, float *distances, uint32_t *counts) const {
+        return handle_ && !gvss_exact_search(handle_, queries, nq, (uint32_t)wanted, (int64_t *)keys, distances, counts);
+    }
+    search_result_t exact_search(const float *query, std::size_t wanted) const {
+        search_result_t r;
+        if (!handle_) { r.error.message = "index was not created: " + create_error_; return r; }
+        if (!wanted) return r;
+        r.keys_.resize(wanted);
+        r.distances_.resize(wanted);
+        uint32_t count = 0;
+        if (gvss_exact_search(handle_, query, 1, (uint32_t)wanted, (int64_t *)r.keys_.data(), r.distances_.data(), &count)) {
+            r.error.message = last_error();
+            count = 0;
+        }
+        r.keys_.resize(count);
+        r.distances_.resize(count);
+        return r;
+    }
+
     labeling_result_t remove(vector_key_t key) {
         labeling_result_t r;
         uint64_t n = 0;
@@ -227,9 +247,13 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         r.completed = n;
         return r;
     }
+    // PRAGMA hnsw_compact_index (hnsw_index.cpp:451-464). Default: usearch's compact() — nodes re-ordered, removed members kept.
+    // GVSS_COMPACT=rebuild: the deleting compaction the extension's README.md:69 describes (gvss_compact_rebuild).
     compaction_result_t compact() {
         compaction_result_t r;
-        if (!handle_ || gvss_compact(handle_)) r.error.message = last_error();
+        const char *mode = std::getenv("GVSS_COMPACT");
+        const bool rebuild = mode && std::strcmp(mode, "rebuild") == 0;
+        if (!handle_ || (rebuild ? gvss_compact_rebuild(handle_, nullptr) : gvss_compact(handle_))) r.error.message = last_error();
         return r;
     }
     // deleting variant (not in usearch): rebuilds the graph over the live members and drops the removed ones

@@ -211,6 +211,15 @@ int gvss_exact_topk_device(char metric, const float *base, uint64_t n, const int
                            uint64_t nq, uint32_t dimensions, uint32_t k, int64_t *ids_out, float *dist_out,
                            void *cuda_stream);
 
+/* The same comparator over the rows an index already holds in HBM (no copy of the base set): exact top-k of nq host queries
+ * among the index's live members, distances = DuckDB's fold of the index metric (array_distance / array_cosine_distance /
+ * array_negative_inner_product, array_kernels.hpp:11-105), keys ascending by (distance, slot); keys_out nq×k (unused tail -1),
+ * dist_out nq×k or NULL, counts_out nq or NULL. It is what `SET hnsw_exact_search = true` (integration/n2_exact_mode.patch)
+ * puts behind HNSW_INDEX_SCAN / HNSW_INDEX_JOIN, i.e. behind the vss_join / vss_match / min_by(.., k) shapes
+ * (hnsw_index_macros.cpp:10-78, hnsw_optimize_topk.cpp:64-219) once an index exists. k + removed members <= 1024. */
+int gvss_exact_search(gvss_index *index, const float *queries, uint64_t nq, uint32_t k, int64_t *keys_out, float *dist_out,
+                      uint32_t *counts_out);
+
 /* --- multi-GPU: merge of per-shard top-k lists after the all-gather (no reference counterpart:
  * the reference is single-process). gathered_*: shards×nq×k on the device, each list ascending; output nq×k
  * ordered by (distance, key). */

@@ -6,4 +6,6 @@ HERE="$(cd "$(dirname "$0")" && pwd)"
 ROOT="$(dirname "$HERE")"
 export LD_LIBRARY_PATH="$HERE/_out:$ROOT/duckdb_vss_b200:${LD_LIBRARY_PATH:-}"
 cd "$HERE/_out" || exit 2
+# this repository's own sqllogictests for the optional patches run from the same test directory
+mkdir -p "$HERE/_out/test/sql" && rm -rf "$HERE/_out/test/sql/gvss" && cp -r "$HERE/test/sql/gvss" "$HERE/_out/test/sql/"
 exec ./unittest --test-dir "$HERE/_out" "${1:-test/sql/hnsw/*}"

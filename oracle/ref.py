@@ -67,9 +67,12 @@ class RefIndex:
         self.h = lib().ref_create(dims, METRIC_CHAR[metric], M, M0, ef_construction, ef_search)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().ref_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().ref_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown
+            pass
 
     def reserve(self, n, threads=1):
         if lib().ref_reserve(self.h, n, threads):

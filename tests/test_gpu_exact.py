@@ -161,3 +161,29 @@ def test_peer_merge_kernel_equals_gathered_merge_single_process():
     with pytest.raises(gv.GvssError, match="256"):
         gvi.merge_topk_peers_device([gk.data_ptr()] * 16, [gd.data_ptr()] * 16, [flags[0].data_ptr()] * 16, 0, 6, nq, 32,
                                     got_k.data_ptr(), got_d.data_ptr())
+
+
+def test_exact_search_over_the_rows_an_index_holds(checker):
+    """gvss_exact_search: brute force over the index's own HBM-resident rows (zero-padded rows, d = 12 -> 16) equals
+    gvss_exact_topk over the host copy, for all three metrics, and skips removed members."""
+    n, d, k = 7000, 12, 10
+    base, q = synth.clustered(n, d, 70, 4, 61, 120)
+    keys = np.arange(n, dtype=np.int64) * 3 + 5
+    for metric in ("l2sq", "cosine", "ip"):
+        ix = gv.Index(d, metric, M=8)
+        ix.reserve(n, 1)
+        ix.add_batch(base, keys=keys)
+        ix.flush()
+        got_k, got_d, got_c = ix.exact_search(q, k)
+        want_k, want_d = gv.exact_topk(metric, base, q, k, keys=keys)
+        np.testing.assert_array_equal(got_k, want_k)
+        np.testing.assert_array_equal(got_d.view(np.uint32), want_d.view(np.uint32))
+        assert (got_c == k).all()
+        gone = want_k[:, 0][:20]
+        for key in set(int(v) for v in gone):
+            assert ix.remove(key) == 1
+        got2, _, c2 = ix.exact_search(q, k)
+        assert not np.isin(got2, gone).any() and (c2 == k).all()
+        live = ~np.isin(keys, gone)
+        want2, _ = gv.exact_topk(metric, base[live], q, k, keys=keys[live])
+        np.testing.assert_array_equal(got2, want2)

@@ -43,16 +43,18 @@ def test_unchanged_extension_sources_compile_against_the_shim():
     assert len(done) == len(srcs)
 
 
-@pytest.mark.parametrize("patch,files", [
-    ("n1_batched_index_join.patch", ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
-    ("n3_streaming_sink.patch", ["src/hnsw/hnsw_index_physical_create.cpp"]),
+@pytest.mark.parametrize("patches,files", [
+    (["n1_batched_index_join.patch"], ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
+    (["n1_batched_index_join.patch", "n2_exact_mode.patch"], ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
+    (["n3_streaming_sink.patch"], ["src/hnsw/hnsw_index_physical_create.cpp"]),
 ])
-def test_operator_patches_apply_to_the_reference_and_compile(tmp_path, patch, files):
+def test_operator_patches_apply_to_the_reference_and_compile(tmp_path, patches, files):
     for f in files:
         os.makedirs(tmp_path / os.path.dirname(f), exist_ok=True)
         shutil.copy(os.path.join(REF, f), tmp_path / f)
-    r = subprocess.run(["patch", "-p1", "-i", os.path.join(ROOT, "integration", patch)], cwd=tmp_path, capture_output=True, text=True)
-    assert r.returncode == 0, r.stdout + r.stderr
+    for patch in patches:
+        r = subprocess.run(["patch", "-p1", "-i", os.path.join(ROOT, "integration", patch)], cwd=tmp_path, capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
     srcs = [str(tmp_path / f) for f in files if f.endswith(".cpp")]
     with ThreadPoolExecutor(max_workers=4) as ex:
         list(ex.map(lambda s: _syntax_check(s, extra_includes=[str(tmp_path / "src" / "include")]), srcs))
