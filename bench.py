@@ -415,6 +415,8 @@ def main():
             s_merge.synchronize()
         torch.cuda.synchronize()
 
+    clocks = ClockSampler(local)   # started before the warm-up: nvidia-smi needs about a second to deliver its first sample
+    clocks.__enter__()
     for _ in range(args.warmup):
         step()
     drain()
@@ -433,17 +435,25 @@ def main():
     l0 = gv.lib().gvss_kernel_launches()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        t_wall0 = time.perf_counter()
-        t_begin.record(s_search)
-        for a, b in ev:
-            a.record(s_search)
+    if len(clocks.rows) < 2:                             # keep the GPU under the same load until the sampler has started
+        t_wait = time.perf_counter()
+        while len(clocks.rows) < 2 and time.perf_counter() - t_wait < 5.0:
             step()
-            b.record(s_search)                           # end of this step's search launch (the merge is on the other stream)
-        (s_merge or s_search).wait_stream(s_search)
-        t_end.record(s_merge or s_search)                # after the last merge AND the last search
-        drain()
-        t_wall = time.perf_counter() - t_wall0
+            drain()
+        if world > 1:
+            dist.barrier()
+    clocks.rows.clear()
+    t_wall0 = time.perf_counter()
+    t_begin.record(s_search)
+    for a, b in ev:
+        a.record(s_search)
+        step()
+        b.record(s_search)                           # end of this step's search launch (the merge is on the other stream)
+    (s_merge or s_search).wait_stream(s_search)
+    t_end.record(s_merge or s_search)                # after the last merge AND the last search
+    drain()
+    t_wall = time.perf_counter() - t_wall0
+    clocks.__exit__(None, None, None)
     launches = gv.lib().gvss_kernel_launches() - l0
     t_dev = t_begin.elapsed_time(t_end) / 1e3                                # whole timed region, device time
     t_kernel = sum(a.elapsed_time(b) for a, b in ev) / 1e3 / args.steps      # search launch alone (roofline)

@@ -319,7 +319,16 @@ static int plan_search(const gvss_index *x, const float *d_queries, uint64_t nq,
     p.sl = make_scratch_layout(limit, x->count, list_cap);
     p.direct = search_mode_bits();
     const bool g4 = setup_gather4(x, p);
-    p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false, g4);
+    // Latency kernel (GVSS_SEARCH_LATENCY=0 switches it off): when the whole batch fits the GPU at once even with a 16 KB row
+    // stage per query, shared memory buys fewer fetch-wait rounds instead of more resident warps (index scans, small joins)
+    static const bool latency_on = [] { const char *e = getenv("GVSS_SEARCH_LATENCY"); return e ? atoi(e) != 0 : true; }();
+    bool latency = false;
+    if (g4 && latency_on && p.direct == 16 && x->dpad > 32) {
+        const SmemLayout big = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, 32u, false, list_cap, 0, false, true, false, 4);
+        if (nq <= resident_warps(x->device, big.bytes, false)) { p.sm = big; p.direct |= 128; latency = true; }
+    }
+    if (!latency)
+        p.sm = make_smem_layout(x->dpad, std::max<uint32_t>(limit, 1), search_heap_smem(x, limit), 0, direct_rows() ? 0u : search_stage_rows(), false, list_cap, search_stage_chunk(), false, g4);
     grid = resident_warps(x->device, p.sm.bytes, false);
     if (!grid) return fail("gvss: no CUDA device");
     static const uint32_t max_warps = [] { const char *e = getenv("GVSS_SEARCH_MAX_WARPS"); return e ? (uint32_t)atoi(e) : 0u; }();

@@ -302,7 +302,10 @@ __device__ __noinline__ float direct_distance(const float *vectors, uint32_t dpa
 // LDS.128 the TMA swizzle (granule ^ row % 8) spreads the lanes over all 8 granules of a line.
 constexpr int kG4Chunk = 32;
 constexpr int kG4OobRow = 0x7FFFFFFF;
-template <int METRIC>
+// NST = 4 KB sub-stages filled per step (all behind one mbarrier phase): 1 for the throughput kernel (shared memory buys
+// resident warps there), 4 for the latency kernel (small batches: a 32-row batch of 512-byte rows is ONE fetch-wait-compute
+// round instead of four).
+template <int METRIC, int NST = 1>
 __device__ __forceinline__ float warp_distances_g4(const GraphView &g, WarpWs &w, uint32_t my_slot, bool active) {
     const uint32_t lane = lane_id();
     const uint32_t amask = __ballot_sync(kFull, active);
@@ -319,23 +322,27 @@ __device__ __forceinline__ float warp_distances_g4(const GraphView &g, WarpWs &w
     float *sbuf = w.stage[0];
     const uint32_t sw = lane & 7u;
     Acc acc = {0.0f, 0.0f, 0.0f};
-    for (uint32_t ch0 = 0; ch0 < nchunks; ch0 += cpt) {
+    for (uint32_t ch0 = 0; ch0 < nchunks; ch0 += cpt * NST) {
         OPCLK(t0);
-        const bool issuer = issuer_row && ch0 + gk < nchunks;
-        const uint32_t nissue = __popc(__ballot_sync(kFull, issuer));
+        uint32_t nissue = 0;
+#pragma unroll
+        for (uint32_t st = 0; st < NST; st++) nissue += __popc(__ballot_sync(kFull, issuer_row && ch0 + st * cpt + gk < nchunks));
         if (lane == 0) mbar_expect_tx(w.mbar, nissue * 4u * kG4Chunk * 4u);
         __syncwarp();
-        if (issuer) tma_gather4(sbuf + lane * kG4Chunk, w.vmap, (int)((ch0 + gk) * kG4Chunk), ra, rb, rc, rd, w.mbar);
+#pragma unroll
+        for (uint32_t st = 0; st < NST; st++)
+            if (issuer_row && ch0 + st * cpt + gk < nchunks)
+                tma_gather4(sbuf + st * 32u * kG4Chunk + lane * kG4Chunk, w.vmap, (int)((ch0 + st * cpt + gk) * kG4Chunk), ra, rb, rc, rd, w.mbar);
         OPCLK(t1);
         mbar_wait(w.mbar, w.phase[0]);
         OPCLK(t2);
         w.phase[0] ^= 1u;
         if (active) {
-            for (uint32_t k = 0; k < cpt && ch0 + k < nchunks; k++) {
-                const uint32_t ch = ch0 + k;
+            for (uint32_t kk = 0; kk < cpt * NST && ch0 + kk < nchunks; kk++) {
+                const uint32_t ch = ch0 + kk, st = kk / cpt, k = kk - st * cpt;
                 const uint32_t nfl = min((uint32_t)kG4Chunk, g.dpad - ch * kG4Chunk);
                 const float4 *a = reinterpret_cast<const float4 *>(w.q + ch * kG4Chunk);
-                const float4 *myrow = reinterpret_cast<const float4 *>(sbuf + (k * rows_cap + lane) * kG4Chunk);
+                const float4 *myrow = reinterpret_cast<const float4 *>(sbuf + st * 32u * kG4Chunk + (k * rows_cap + lane) * kG4Chunk);
                 if (nfl == kG4Chunk) {
 #pragma unroll
                     for (uint32_t i = 0; i < kG4Chunk / 4; i++) {
@@ -371,11 +378,13 @@ struct LeftSrc {
 // (neighbour-selection steps) do not touch HBM/L2 again when a row is a single chunk.
 // MODE = 1: the production search configuration is fixed at compile time — query-to-node distances through gather4
 // staging, whole-row and visited-window prefetches on, list-as-queue allowed — so none of the alternative paths (kept for
-// A/B measurements and for the build) takes part in k_search's register allocation. MODE = 0: configuration from WarpWs.
+// A/B measurements and for the build) takes part in k_search's register allocation. MODE = 2: the same with a 16 KB stage
+// (latency kernel for batches that fit the GPU at once). MODE = 0: configuration from WarpWs.
 template <int METRIC, int MODE = 0>
 __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, LeftSrc left, uint32_t my_slot,
                                                 bool active, uint32_t &staged) {
-    if (MODE == 1) return warp_distances_g4<METRIC>(g, w, my_slot, active);
+    if (MODE == 1) return warp_distances_g4<METRIC, 1>(g, w, my_slot, active);
+    if (MODE == 2) return warp_distances_g4<METRIC, 4>(g, w, my_slot, active); // latency kernel: 16 KB stage
     const uint32_t lane = lane_id();
     const uint32_t chunk = w.chunk;
     const uint32_t nchunks = (g.dpad + chunk - 1) / chunk;
@@ -782,8 +791,8 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                                             uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged, bool lq = false) {
     const uint32_t lane = lane_id();
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const bool cfg_g4 = MODE == 1 ? true : w.g4, cfg_pf_rows = MODE == 1 ? true : w.prefetch_rows,
-               cfg_pf_vis = MODE == 1 ? true : w.prefetch_vis, cfg_spec = MODE == 1 ? false : w.spec_prefetch;
+    const bool cfg_g4 = MODE != 0 ? true : w.g4, cfg_pf_rows = MODE != 0 ? true : w.prefetch_rows,
+               cfg_pf_vis = MODE != 0 ? true : w.prefetch_vis, cfg_spec = MODE != 0 ? false : w.spec_prefetch;
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
     uint32_t scan_from = 0; // LQ: every list entry before this index is expanded

@@ -20,7 +20,7 @@ struct SmemLayout {
 // several chunks (build), else the chunks are staged one after the other into one buffer (search: half the footprint)
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
                             bool with_left, uint32_t list_cap, uint32_t chunk = 0, bool double_buffer = true, bool gather4 = false,
-                            bool g4_alias = false);
+                            bool g4_alias = false, uint32_t g4_stages = 1);
 // tensor map for the gather4 staging path (exact_tc.cu holds the driver entry point); false when the driver refuses
 bool encode_row_gather_map(CUtensorMap *m, const float *vectors, uint64_t rows, uint32_t dpad);
 uint32_t default_heap_smem(uint32_t beam);
@@ -54,7 +54,8 @@ struct SearchParams {
     int direct;            // bit0: stream rows into registers instead of staging them; bit1: speculative row prefetch;
                            // bit2: stage with cp.async instead of TMA; bit3: always use usearch's heap as the queue;
                            // bit4: rows staged by TMA gather4 (4 rows per instruction) through `vmap`, 32 rows x 32 floats per step;
-                           // bit5: no whole-row L2 prefetch at the start of a hop
+                           // bit5: no whole-row L2 prefetch at the start of a hop; bit6: no visited-window prefetch;
+                           // bit7: latency kernel — 16 KB gather4 stage, batches that fit the GPU at once (k_search<METRIC, 2>)
 };
 // grid = number of resident warps; returns cudaError
 cudaError_t launch_search(int metric, const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t stream);

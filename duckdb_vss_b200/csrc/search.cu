@@ -53,7 +53,7 @@ __device__ __forceinline__ void carve(WarpWs &w, unsigned char *smem, const Smem
 #define GVSS_SEARCH_MIN_BLOCKS 24
 #endif
 // MODE: see warp_distances (hnsw_device.cuh). launch_search picks MODE 1 whenever the run-time configuration is the default one.
-template <int METRIC, int MODE> __global__ void __launch_bounds__(32, GVSS_SEARCH_MIN_BLOCKS) k_search(GraphView g, const __grid_constant__ SearchParams p) {
+template <int METRIC, int MODE> __global__ void __launch_bounds__(32, MODE == 2 ? 8 : GVSS_SEARCH_MIN_BLOCKS) k_search(GraphView g, const __grid_constant__ SearchParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     WarpWs w;
     carve(w, smem, p.sm, p.scratch, p.sl, p.direct, &p.vmap);
@@ -69,7 +69,7 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32, GVSS_SEARC
         const float *qsrc = p.queries + qi * (p.query_stride ? p.query_stride : g.dims);
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = i < g.dims ? __ldg(qsrc + i) : 0.0f;
         __syncwarp();
-        if (METRIC == kCos && (MODE == 1 || w.g4)) w.q_a2 = fold_a2(w.q, g.dpad);
+        if (METRIC == kCos && (MODE != 0 || w.g4)) w.q_a2 = fold_a2(w.q, g.dpad);
 
         Counters cnt = {0, 0, 0, (long long)qi == p.trace_query ? 0x80000000u : 0u};
         uint32_t top_size = 0;
@@ -89,7 +89,7 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32, GVSS_SEARC
             // list-as-queue first (hashed visited table); a query that would overfill the table is redone with the exact
             // bitmap (flag bit1); exact ties switch to usearch's heap mid-flight (flag bit2), or — if the operation log ran
             // out of room — repeat the query with the heap from the start
-            const bool lq_ok = MODE == 1 || (p.direct & 8) == 0;
+            const bool lq_ok = MODE != 0 || (p.direct & 8) == 0;
             bool lq = lq_ok, bitmap = false;
             OPCLK(t_q0);
             for (;;) {
@@ -124,8 +124,9 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32, GVSS_SEARC
 }
 
 SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem, uint32_t misc_bytes, uint32_t stage_rows,
-                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer, bool gather4, bool g4_alias) {
+                            bool with_left, uint32_t list_cap, uint32_t chunk, bool double_buffer, bool gather4, bool g4_alias, uint32_t g4_stages) {
     SmemLayout s{};
+    if (g4_stages != 4) g4_stages = 1;
     if (chunk == 0 || chunk > (uint32_t)kChunk) chunk = (uint32_t)kChunk;
     if (gather4) { chunk = kG4Chunk; stage_rows = 32; double_buffer = false; }
     const uint32_t chunkf = dpad < chunk ? dpad : chunk;
@@ -133,7 +134,7 @@ SmemLayout make_smem_layout(uint32_t dpad, uint32_t top_cap, uint32_t heap_smem,
     s.rstride = chunkf + (((chunkf / 4) % 2 == 0) ? 4u : 0u); // odd number of 16-byte granules per row
     if (gather4) s.rstride = kG4Chunk;                         // dense 128-byte rows, conflicts removed by the TMA swizzle
     s.stage_rows = stage_rows;
-    const uint32_t stage_bytes = stage_rows * s.rstride * 4u;
+    const uint32_t stage_bytes = stage_rows * s.rstride * 4u * (gather4 ? g4_stages : 1u);
     const bool two = double_buffer && dpad > chunkf;
     s.nbuf = two ? 2u : 1u;
     uint32_t off = 0;
@@ -224,7 +225,9 @@ template <int METRIC, int MODE> static cudaError_t launch_search_tm(const GraphV
 template <int METRIC> static cudaError_t launch_search_t(const GraphView &g, const SearchParams &p, uint32_t grid, cudaStream_t st) {
     // p.direct == 16: gather4 staging and nothing else switched away from its default (GVSS_SEARCH_GENERIC=1 forces MODE 0)
     static const bool generic = [] { const char *e = getenv("GVSS_SEARCH_GENERIC"); return e && atoi(e); }();
-    return (p.direct == 16 && !generic) ? launch_search_tm<METRIC, 1>(g, p, grid, st) : launch_search_tm<METRIC, 0>(g, p, grid, st);
+    if ((p.direct & ~128) == 16 && !generic) // bit7: latency kernel (the host laid out a 16 KB stage)
+        return (p.direct & 128) ? launch_search_tm<METRIC, 2>(g, p, grid, st) : launch_search_tm<METRIC, 1>(g, p, grid, st);
+    return launch_search_tm<METRIC, 0>(g, p, grid, st);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
