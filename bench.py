@@ -435,13 +435,20 @@ def main():
     l0 = gv.lib().gvss_kernel_launches()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if len(clocks.rows) < 2:                             # keep the GPU under the same load until the sampler has started
-        t_wait = time.perf_counter()
-        while len(clocks.rows) < 2 and time.perf_counter() - t_wait < 5.0:
-            step()
-            drain()
+    # keep the GPUs under the same load until every rank's sampler delivers (all ranks take the same number of extra steps: the
+    # peer exchange counts them)
+    t_wait = time.perf_counter()
+    while True:
+        need = torch.tensor([int(len(clocks.rows) < 2 and time.perf_counter() - t_wait < 5.0)], dtype=torch.int32, device=dev)
         if world > 1:
-            dist.barrier()
+            dist.all_reduce(need, op=dist.ReduceOp.MAX)
+        if not int(need.item()):
+            break
+        step()
+        drain()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
     clocks.rows.clear()
     t_wall0 = time.perf_counter()
     t_begin.record(s_search)
