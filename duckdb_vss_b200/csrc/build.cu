@@ -14,14 +14,12 @@
 namespace gvss {
 
 __device__ __forceinline__ void carve_build(WarpWs &w, unsigned char *smem, const SmemLayout &sm, uint8_t *scratch,
-                                            const ScratchLayout &sl, int direct, const CUtensorMap *vmap) {
-    // node-to-node distances (neighbour selection) stage whole rows; the query-to-node distances of the insert-time searches
-    // go through gather4 staging like k_search when the host provided a tensor map (direct bit4): the gather4 stage is the first
-    // 4 KB of the row stage
-    w.g4 = (direct & 16) != 0;
-    w.vmap = vmap;
+                                            const ScratchLayout &sl, int direct) {
+    w.g4 = false; // the build stages whole rows (neighbour selection re-reads them); gather4 staging for its query-to-node
+                  // distances was measured (+1.6 % at best, profiles/r3_build_ab.txt) and taken out again
+    w.vmap = nullptr;
     w.q_a2 = 0.0f;
-    w.prefetch_rows = w.g4;
+    w.prefetch_rows = false;
     w.prefetch_vis = (direct & 64) == 0;
     w.direct = (direct & 1) != 0;
     w.spec_prefetch = (direct & 2) != 0;
@@ -170,10 +168,10 @@ __device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t
     unlock_node(locks, target);
 }
 
-template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g, const __grid_constant__ BuildParams p) {
-    extern __shared__ __align__(1024) unsigned char smem[];
+template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
     WarpWs w;
-    carve_build(w, smem, p.sm, p.scratch, p.sl, p.direct, &p.vmap);
+    carve_build(w, smem, p.sm, p.scratch, p.sl, p.direct);
     const uint32_t lane = lane_id();
     const uint32_t cmax = max(g.M, g.M0);
     uint32_t *mine_s = reinterpret_cast<uint32_t *>(smem + p.sm.off_misc);
@@ -194,7 +192,6 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         for (uint32_t i = lane; i < g.dpad; i += 32) w.q[i] = g.vectors[(size_t)slot * g.dpad + i];
         if (p.inflight && lane == 0) __stcg(p.inflight + blockIdx.x, slot);
         __syncwarp();
-        if (METRIC == kCos && w.g4) w.q_a2 = fold_a2(w.q, g.dpad);
 
         unsigned long long es = 0;
         if (lane == 0) {

@@ -1600,11 +1600,8 @@ static int flush_locked(gvss_index *x) {
     p.direct = search_mode_bits();
     // with the list-as-queue beam search the heap only serves exact ties: 32 entries (its 5 top levels) stay in shared memory
     const uint32_t build_heap = (p.direct & 8) ? default_heap_smem(p.ef_add) : 32u;
-    // query-to-node distances through gather4 staging (as in k_search) unless switched off (GVSS_BUILD_GATHER4=0)
-    static const bool build_g4 = [] { const char *e = getenv("GVSS_BUILD_GATHER4"); return e ? atoi(e) != 0 : true; }();
-    p.direct &= ~16;
-    if (build_g4 && gather4_rows() && stage_with_tma() && !direct_rows() && x->dpad >= 32 && encode_row_gather_map(&p.vmap, x->d_vectors, x->capacity, x->dpad)) p.direct |= 16;
-    p.sm = make_smem_layout(x->dpad, top_cap, build_heap, (2 * cmax + 2) * 8, build_rows, true, cmax, 0, true, false, (p.direct & 16) != 0);
+    p.direct &= ~16; // gather4 staging is a search path
+    p.sm = make_smem_layout(x->dpad, top_cap, build_heap, (2 * cmax + 2) * 8, build_rows, true, cmax);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (!max_warps) { give_back(); return fail("gvss: no CUDA device"); }
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;

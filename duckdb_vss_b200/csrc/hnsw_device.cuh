@@ -392,8 +392,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
-    // gather4 staging serves the QUERY-to-node distances only (the build also passes left-hand rows that sit in the row stage)
-    if (w.g4 && left.smem == w.q) { staged = kInvalid; return warp_distances_g4<METRIC>(g, w, my_slot, active); } // (the gather4 stage overlays the row stage)
+    if (w.g4 && left.smem == w.q) return warp_distances_g4<METRIC>(g, w, my_slot, active); // gather4 staging serves query-to-node distances only
 #if GVSS_DIRECT_PATH
     if (w.direct && !stream_left) { // no staging at all: all 32 lanes at once
         const float d = direct_distance<METRIC>(g.vectors, g.dpad, left.smem, my_slot, active);

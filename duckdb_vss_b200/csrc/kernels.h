@@ -83,7 +83,6 @@ struct BuildParams {
     uint8_t *scratch;
     ScratchLayout sl;
     SmemLayout sm;
-    alignas(64) CUtensorMap vmap; // direct bit4: query-to-node distances of the insert-time searches stage rows by TMA gather4 through this map
 };
 cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t stream);
 

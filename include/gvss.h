@@ -166,7 +166,9 @@ int gvss_search_device(gvss_index *index, const float *queries, uint64_t nq, uin
  *    than the GPU could run at once, the call is correct but slower than gvss_search_device.
  *  - Rows staged by gvss_add* must have been inserted with gvss_flush beforehand (flushing allocates; this call
  *    refuses instead).
- *  - The first call on each device resolves the array's device address; make that call before any stream capture.
+ *  - The first call on each device resolves the array's device address and, like any first launch, loads the search kernel's
+ *    module (the driver may allocate for that): make one warm-up call before any stream capture and before counting on
+ *    "no allocation".
  *  - All calls on one GPU share the array and it keeps the previous call's contents: the library clears what must
  *    start clean, but two calls that overlap on the GPU (different streams or threads) race and corrupt each other.
  *    Serialise them. */

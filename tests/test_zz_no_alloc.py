@@ -56,3 +56,34 @@ def test_noalloc_rejects_what_does_not_fit_and_staged_rows():
     iy.add(1, np.zeros(3, np.float32))
     with pytest.raises(gv.GvssError, match="gvss_flush"):
         iy.search_device_noalloc(q.data_ptr(), 1, 1, 8, out.data_ptr())
+
+
+def test_noalloc_search_leaves_free_device_memory_untouched():
+    """The property the entry point exists for: once its one-time set-up has run (first call on the device: the address of the
+    built-in scratch array is looked up and the search kernel's module is loaded), further calls take no device memory at all —
+    free memory as the driver reports it and the index's own accounting stay exactly where they were — also when a larger beam
+    or another index re-uses the array the previous call left dirty."""
+    import torch
+    z, blob = load_golden("clustered40_l2sq")
+    ix = gv.Index(z["base"].shape[1], "l2sq", M=int(z["M"]), M0=int(z["M0"]), ef_construction=int(z["efc"]))
+    ix.load(blob)
+    z2, blob2 = load_golden("clustered16_l2sq")
+    iy = gv.Index(z2["base"].shape[1], "l2sq", M=int(z2["M"]), M0=int(z2["M0"]), ef_construction=int(z2["efc"]))
+    iy.load(blob2)
+    q, q2 = torch.from_numpy(z["queries"]).cuda(), torch.from_numpy(z2["queries"]).cuda()
+    nq = max(q.shape[0], q2.shape[0])
+    keys = torch.empty((nq, 10), dtype=torch.int64, device="cuda")
+    dist = torch.empty((nq, 10), dtype=torch.float32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    for index, queries in ((ix, q), (iy, q2)):   # warm-up: one-time set-up per device, kernel module loaded
+        index.search_device_noalloc(queries.data_ptr(), queries.shape[0], 10, 16, keys.data_ptr(), dist.data_ptr(), 0, 0, st)
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    use0 = (ix.info()["memory_usage"], iy.info()["memory_usage"])
+    for ef in (10, 64, 128, 64):                  # smaller beam, larger beam (another table layout over the dirty array), back
+        for index, queries, zz in ((ix, q, z), (iy, q2, z2)):
+            index.search_device_noalloc(queries.data_ptr(), queries.shape[0], 10, ef, keys.data_ptr(), dist.data_ptr(), 0, 0, st)
+            torch.cuda.synchronize()
+            np.testing.assert_array_equal(keys[:queries.shape[0]].cpu().numpy(), zz[f"keys_ef{ef}"])
+    assert torch.cuda.mem_get_info()[0] == free0
+    assert (ix.info()["memory_usage"], iy.info()["memory_usage"]) == use0
