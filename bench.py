@@ -49,7 +49,14 @@ WORKLOADS = {
                "clustered(C=N/100, r=16) seed 42 (SURVEY.md App. D law, numpy)"),
     "deep10m": ("10M x FLOAT[96] ip (Deep10M shape) partitioned over the GPUs, 10k-query batch, k=10", "ip", 96, 10_000_000,
                 "clustered(C=N/100, r=24) seed 46, L2-normalised (SURVEY.md §8d config 4, numpy)"),
+    "text768": ("1M x FLOAT[768] cosine (text-embedding shape), 10k-query batch, k=10", "cosine", 768, 1_000_000,
+                "clustered(C=N/100, r=32) seed 44, rows L2-normalised then scaled by U(0.5, 2) (SURVEY.md §8d config 3, numpy)"),
+    "join10m": ("index join / exact top-k: 100k queries x 10M x FLOAT[128] l2sq, k=10", "l2sq", 128, 10_000_000,
+                "clustered(C=N/100, r=16) seed 48 (SURVEY.md §8d config 5, numpy)"),
 }
+DEFAULT_NQ = {"join10m": 100_000}
+# the 10M-row sets need wider beams than the 1M sets to reach the gate
+EF_SWEEP_WIDE = EF_SWEEP + (768, 1024, 1536, 2048)
 
 
 def peaks():
@@ -118,8 +125,8 @@ def algorithmic_bytes(stats, d, M, M0, k):
 def make_data(workload, n_total, nq):
     """(base[n_total, d], queries[nq, d]) of the named workload, deterministic."""
     from duckdb_vss_b200 import synth
-    if workload == "deep10m":
-        c = synth.config("deep10m", n=n_total, nq=nq)
+    if workload in ("deep10m", "text768", "join10m"):
+        c = synth.config(workload, n=n_total, nq=nq)
         return c["base"], c["queries"]
     return synth.clustered(n_total, 128, max(1024, n_total // 100), 16, 42, nq)
 
@@ -133,7 +140,7 @@ def run_reference(args):
         return
     label, metric, d, n_default, gen = WORKLOADS["sift1m"]
     n = args.n or n_default
-    nq, k = args.nq, 10
+    nq, k = args.nq or 10_000, 10
     if oracle.have_ref():
         from oracle import ref as impl
         kind, Index, threads = "reference", impl.RefIndex, impl.hardware_threads()
@@ -234,7 +241,7 @@ def main():
     ap.add_argument("--impl", default="gvss", choices=["gvss", "reference"])
     ap.add_argument("--workload", default="sift1m", choices=sorted(WORKLOADS))
     ap.add_argument("--vectors", dest="n", type=int, default=0, help="base vectors (per GPU for sift1m, in total for deep10m); 0 = the config's size")
-    ap.add_argument("--nq", type=int, default=10_000)
+    ap.add_argument("--nq", type=int, default=0, help="queries per step; 0 = the config's batch (10 000; join10m: 100 000)")
     ap.add_argument("--ef", type=int, default=0, help="0 = smallest ef of the sweep with recall@10 >= 0.95")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
@@ -260,8 +267,9 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     label, metric, d, n_default, gen = WORKLOADS[args.workload]
-    strong = args.workload == "deep10m"
-    nq, k, M, M0 = args.nq, 10, M_BENCH, M0_BENCH
+    strong = args.workload != "sift1m"     # ONE named set, partitioned over the ranks when there are several
+    nq, k, M, M0 = args.nq or DEFAULT_NQ.get(args.workload, 10_000), 10, M_BENCH, M0_BENCH
+    ef_sweep = EF_SWEEP_WIDE if args.workload == "join10m" else EF_SWEEP
     if strong:
         # ONE set partitioned by contiguous row ranges; keys = global row numbers
         n_total = args.n or n_default
@@ -341,7 +349,7 @@ def main():
     # ---- operating point: smallest ef of the sweep whose recall@10 (of the merged list, N > 1) is >= 0.95 ---------------
     sweep, shard_sweep = {}, {}
     ef = args.ef
-    for e in ([args.ef] if args.ef else EF_SWEEP):
+    for e in ([args.ef] if args.ef else ef_sweep):
         search(e)
         if world > 1:
             nccl_merge(mk, md)
@@ -581,7 +589,7 @@ def main():
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": label, "generator": gen, "n_per_gpu": n, "n_total": n_total,
                        "queries_per_step": nq, "k": k, "ef_search": ef, "recall_at_10": recall, "ef_sweep": sweep,
-                       "M": M, "M0": M0, "ef_construction": EFC_BENCH,
+                       "M": M, "M0": M0, "ef_construction": EFC_BENCH, "recall_gate_met": bool(recall >= 0.95),
                        "units": ("queries answered by the whole job (each query is searched on every shard of the one partitioned set)" if strong
                                  else "per-shard query searches summed over ranks (every query visits every shard)"),
                        "global_queries_per_s": nq * args.steps / t_dev,
