@@ -236,6 +236,23 @@ struct TempDev {
     }
 };
 
+// two pinned bounce buffers with an event each (persistence: copies overlap the stream callback)
+struct PinnedPair {
+    void *buf[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    ~PinnedPair() {
+        for (int i = 0; i < 2; i++) { if (buf[i]) cudaFreeHost(buf[i]); if (ev[i]) cudaEventDestroy(ev[i]); }
+    }
+    cudaError_t alloc(size_t bytes) {
+        for (int i = 0; i < 2; i++) {
+            cudaError_t e = cudaMallocHost(&buf[i], bytes ? bytes : 1);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    }
+};
+
 // heap entries held in shared memory on the search path (GVSS_HEAP_SMEM overrides default_heap_smem for experiments)
 // With the list-as-queue search (no removed members) the heap only serves the rare exact-tie replay and lives in global
 // scratch entirely: the 2 KB it would take per query buy more resident queries.
@@ -1051,13 +1068,23 @@ int gvss_save(gvss_index *x, int (*write)(void *, const void *, size_t), void *u
     uint32_t hdr[2] = {(uint32_t)n, d * 4};
     if (!write(user, hdr, 8)) return fail("gvss_save: output callback failed");
     {
-        const uint64_t rows_per = std::max<uint64_t>(1, (32ull << 20) / (d * 4ull));
-        std::vector<float> buf(std::min(rows_per, std::max<uint64_t>(n, 1)) * d);
-        for (uint64_t r = 0; r < n; r += rows_per) {
-            const uint64_t m = std::min(rows_per, n - r);
-            CU(cudaMemcpy2DAsync(buf.data(), d * 4ull, x->d_vectors + r * x->dpad, x->dpad * 4ull, d * 4ull, m, cudaMemcpyDeviceToHost, st));
-            CU(cudaStreamSynchronize(st));
-            if (!write(user, buf.data(), m * d * 4ull)) return fail("gvss_save: output callback failed");
+        // two pinned buffers: while the callback consumes one chunk the next one is already on its way from the GPU
+        const uint64_t rows_per = std::max<uint64_t>(1, (16ull << 20) / (d * 4ull));
+        const uint64_t chunk_rows = std::min(rows_per, std::max<uint64_t>(n, 1));
+        PinnedPair pin;
+        CU(pin.alloc(chunk_rows * d * 4ull));
+        auto fetch = [&](uint64_t r, int b) -> cudaError_t {
+            const uint64_t m = std::min(chunk_rows, n - r);
+            cudaError_t e = cudaMemcpy2DAsync(pin.buf[b], d * 4ull, x->d_vectors + r * x->dpad, x->dpad * 4ull, d * 4ull, m, cudaMemcpyDeviceToHost, st);
+            return e == cudaSuccess ? cudaEventRecord(pin.ev[b], st) : e;
+        };
+        if (n) CU(fetch(0, 0));
+        int b = 0;
+        for (uint64_t r = 0; r < n; r += chunk_rows, b ^= 1) {
+            const uint64_t m = std::min(chunk_rows, n - r);
+            if (r + chunk_rows < n) CU(fetch(r + chunk_rows, b ^ 1));
+            CU(cudaEventSynchronize(pin.ev[b]));
+            if (!write(user, pin.buf[b], m * d * 4ull)) return fail("gvss_save: output callback failed");
         }
     }
     // (2) 64-byte dense header (index_dense.hpp:46-83,850-874)
@@ -1116,14 +1143,20 @@ static int load_into(gvss_index *y, int (*read)(void *, void *, size_t), void *u
     const uint32_t d = y->cfg.dimensions;
     if (ensure_capacity(y, std::max<uint64_t>(n, 1))) return 1;
     {
-        const uint64_t rows_per = std::max<uint64_t>(1, (32ull << 20) / (d * 4ull));
-        std::vector<float> buf(std::min(rows_per, std::max<uint64_t>(n, 1)) * d);
-        for (uint64_t r = 0; r < n; r += rows_per) {
-            const uint64_t m = std::min(rows_per, n - r);
-            if (!read(user, buf.data(), m * d * 4ull)) return fail("gvss_load: truncated vectors");
-            CU(cudaMemcpy2DAsync(y->d_vectors + r * y->dpad, y->dpad * 4ull, buf.data(), d * 4ull, d * 4ull, m, cudaMemcpyHostToDevice, y->stream));
-            CU(cudaStreamSynchronize(y->stream));
+        // the stream is read straight into pinned memory, two buffers: the upload of one chunk overlaps the read of the next
+        const uint64_t rows_per = std::max<uint64_t>(1, (16ull << 20) / (d * 4ull));
+        const uint64_t chunk_rows = std::min(rows_per, std::max<uint64_t>(n, 1));
+        PinnedPair pin;
+        CU(pin.alloc(chunk_rows * d * 4ull));
+        int b = 0;
+        for (uint64_t r = 0; r < n; r += chunk_rows, b ^= 1) {
+            const uint64_t m = std::min(chunk_rows, n - r);
+            CU(cudaEventSynchronize(pin.ev[b])); // the upload that read this buffer two chunks ago
+            if (!read(user, pin.buf[b], m * d * 4ull)) return fail("gvss_load: truncated vectors");
+            CU(cudaMemcpy2DAsync(y->d_vectors + r * y->dpad, y->dpad * 4ull, pin.buf[b], d * 4ull, d * 4ull, m, cudaMemcpyHostToDevice, y->stream));
+            CU(cudaEventRecord(pin.ev[b], y->stream));
         }
+        CU(cudaStreamSynchronize(y->stream));
     }
     uint8_t head[64];
     if (!read(user, head, 64)) return fail("gvss_load: truncated header");

@@ -58,3 +58,16 @@ def test_background_build_overlaps_the_feeding_threads(tmp_path):
     assert streamed < one_shot                      # the build overlapped the scan ...
     assert streamed < scan + 0.6 * (one_shot - scan)  # ... for more than a third of its duration
     assert abs(r1 - r2) < 0.01 and r2 > 0.9
+
+
+def test_persistence_round_trip_through_callbacks_is_pipelined_and_exact(tmp_path):
+    """gvss_save / gvss_load through in-memory callbacks (the shape of HNSWIndex::PersistToDisk / the loading constructor,
+    hnsw_index.cpp:193-206, 510-532): the stream has exactly serialized_length bytes and the reloaded index answers alike."""
+    exe = str(tmp_path / "persist_driver")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    subprocess.run(["g++", "-std=c++17", "-O2", f"-I{ROOT}/include", f"{ROOT}/tests/cpp/persist_driver.cpp", f"-L{libdir}", "-lgvss",
+                    f"-Wl,-rpath,{libdir}", "-o", exe], check=True)
+    out = subprocess.run([exe, "150000", "96"], check=True, capture_output=True, text=True, timeout=600).stdout
+    print(out)
+    m = re.search(r"stream_bytes (\d+) serialized_length (\d+) save_s ([0-9.]+) .* load_s ([0-9.]+) .* same_results 1", out)
+    assert m and m.group(1) == m.group(2), out
