@@ -11,10 +11,14 @@ def readme_grid():
     return np.array([(a, b, c) for a in range(1, 10) for b in range(1, 10) for c in range(1, 10)], dtype=np.float32)
 
 
-def clustered(n, d, C, r, seed, n_queries=0, sigma=0.35, noise=0.05, chunk=262144):
+def clustered(n, d, C, r, seed, n_queries=0, sigma=0.35, noise=0.05, chunk=262144, point_seed=None):
+    """``point_seed``: draw the points from a stream of their own while centres and projection still come from ``seed`` —
+    another sample of the SAME data set (the shards of one partitioned base set), not another data set."""
     rng = np.random.default_rng(seed)
     centres = rng.standard_normal((C, d), dtype=np.float32)
     proj = (sigma * rng.standard_normal((r, d), dtype=np.float32)).astype(np.float32)
+    if point_seed is not None:
+        rng = np.random.default_rng(point_seed)
 
     def draw(m):
         out = np.empty((m, d), dtype=np.float32)
