@@ -10,6 +10,7 @@
 // only while its list is rewritten; a warp never holds two locks, so there is no lock-order deadlock.
 // With one warp (concurrency 1) the kernel reproduces the reference's single-thread build byte for byte.
 #include "kernels.h"
+#include <cstdlib>
 
 namespace gvss {
 
@@ -73,7 +74,7 @@ __device__ __forceinline__ void unlock_node(uint32_t *locks, uint32_t s) {
 
 // refine_ (index.hpp:3602-3638). Candidates = w.top_* [0, ncand) ascending. Keeps c iff for every already kept s:
 // !(d(c, s) < d(c, q)). Lanes hold 32 consecutive candidates; each kept node costs one batch of distances.
-template <int METRIC>
+template <int METRIC, int MODE>
 __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32_t ncand, uint32_t needed,
                                            uint32_t *kept_s, float *kept_d, uint32_t &staged) {
     const uint32_t lane = lane_id();
@@ -93,7 +94,7 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
             const uint32_t am0 = __ballot_sync(kFull, alive);
             if (!am0) break;
             w.n_pair += __popc(am0);
-            const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, kept_s[k]}, cs, alive, staged);
+            const float d = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, kept_s[k]}, cs, alive, staged);
             if (alive && d < cd) alive = false;
         }
         uint32_t amask = __ballot_sync(kFull, alive);
@@ -113,7 +114,7 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
                 // step needs no memory access at all
                 const bool resident = g.dpad <= (uint32_t)kChunk && w.stage_rows == 32 && __shfl_sync(kFull, staged, j) == sj;
                 const LeftSrc left = resident ? LeftSrc{w.stage[0] + j * w.rstride, 0} : LeftSrc{nullptr, sj};
-                const float d = warp_distances<METRIC>(g, w, left, cs, act, staged);
+                const float d = warp_distances<METRIC, MODE>(g, w, left, cs, act, staged);
                 if (act && d < cd) alive = false;
             }
             amask = __ballot_sync(kFull, alive && lane > j);
@@ -125,7 +126,7 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
 // One directed link update under the target's lock: append `nbr` to `target`'s list on `level`, or, when the list is
 // full, re-run the heuristic over {(d_tn, nbr)} ∪ {(d(target, x), x)} with needed = capacity
 // (reconnect_neighbor_nodes_, index.hpp:3279-3311). `d_tn` = d(target, nbr).
-template <int METRIC>
+template <int METRIC, int MODE>
 __device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t *locks, uint32_t target, uint32_t nbr, float d_tn,
                                          int level, uint32_t *kept_s, float *kept_d, uint32_t top_limit_all, uint32_t &staged,
                                          bool count_d_tn = false) {
@@ -156,19 +157,21 @@ __device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t
         const uint32_t am = __ballot_sync(kFull, act);
         if (!am) break;
         w.n_pair += __popc(am);
-        const float d = warp_distances<METRIC>(g, w, LeftSrc{nullptr, target}, e, act, staged);
+        const float d = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, target}, e, act, staged);
         for (uint32_t m = am; m; m &= m - 1) {
             const uint32_t j = __ffs(m) - 1;
             top_insert(w, tsz, top_limit_all, __shfl_sync(kFull, d, j), __shfl_sync(kFull, e, j));
         }
     }
-    const uint32_t nk2 = refine<METRIC>(g, w, tsz, capc, kept_s, kept_d, staged);
+    const uint32_t nk2 = refine<METRIC, MODE>(g, w, tsz, capc, kept_s, kept_d, staged);
     for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
     w.n_rows_written++;
     unlock_node(locks, target);
 }
 
-template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
+// MODE 3 = the production configuration fixed at compile time (32-row stage, TMA bulk copies, prefetches as shipped): the A/B
+// paths stay out of the kernel, which is otherwise large enough to stall on instruction fetch; MODE 0 = run-time knobs.
+template <int METRIC, int MODE> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     WarpWs w;
     carve_build(w, smem, p.sm, p.scratch, p.sl, p.direct);
@@ -216,7 +219,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
         w.n_rows_written = 0;
         uint32_t n_qdist = 0, n_base = 0;
         long long t0 = clock64(), t_beam = 0, t_refine = 0, t_conn = 0, t_recon = 0;
-        uint32_t closest = greedy_descent<METRIC, true>(g, w, entry, max_level, level, cnt, staged);
+        uint32_t closest = greedy_descent<METRIC, true, MODE>(g, w, entry, max_level, level, cnt, staged);
         const long long t_greedy = clock64() - t0;
 
         for (int l = min(level, max_level); l >= 0; --l) {
@@ -224,12 +227,12 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             t0 = clock64();
             // list-as-queue first; a level that would overfill the visited table is redone with the exact bitmap; exact ties
             // switch to usearch's heap mid-flight (same scheme as k_search)
-            bool lq = (p.direct & 8) == 0, bitmap = false;
+            bool lq = MODE == 3 || (p.direct & 8) == 0, bitmap = false;
             const uint32_t base_before = cnt.base;
             for (;;) {
                 cnt.flags = 0;
                 w.use_bitmap = bitmap;
-                beam_search<METRIC, true, true>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged, lq);
+                beam_search<METRIC, true, true, MODE>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged, lq);
                 if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
                 if (cnt.flags & 8u) { lq = false; continue; }
                 break;
@@ -242,7 +245,7 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
             // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)
             const uint32_t cap_l = l ? g.M : g.M0;
             t_beam += clock64() - t0; t0 = clock64();
-            uint32_t nk = refine<METRIC>(g, w, top_size, g.M, kept_s, kept_d, staged);
+            uint32_t nk = refine<METRIC, MODE>(g, w, top_size, g.M, kept_s, kept_d, staged);
             nk = min(nk, cap_l);
             t_refine += clock64() - t0; t0 = clock64();
             for (uint32_t i = lane; i < nk; i += 32) { mine_s[i] = kept_s[i]; mine_d[i] = kept_d[i]; }
@@ -270,32 +273,51 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
 
             // reconnect_neighbor_nodes_
             const float a_worst = nk ? kept_d[nk - 1] : CUDART_INF_F; // distance of this node's farthest own link
-            for (uint32_t i = 0; i < nk; i++) {
-                const uint32_t close = mine_s[i];
-                if (close == slot) continue;
-                float dn = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
-                dn = __shfl_sync(kFull, dn, 0);
-                add_link<METRIC>(g, w, p.locks, close, slot, dn, l, kept_s, kept_d, top_limit_all, staged, true);
-            }
-            // Inserts that are in flight at the same time cannot find each other through the graph. Before this node
-            // leaves, it measures its distance to every vector other warps are inserting right now and links both ways with
-            // those that are closer than its farthest own link (same append / re-prune rule as any reverse link). With one
-            // insert in flight the list is empty and the build stays byte-identical to the reference's single-thread build.
-            if (l == 0 && p.inflight && gridDim.x > 1) {
-                for (uint32_t base = 0; base < gridDim.x; base += 32) {
-                    const uint32_t wi = base + lane;
-                    const uint32_t x = wi < gridDim.x ? __ldcg(p.inflight + wi) : kInvalid;
-                    const bool act = x != kInvalid && x != slot && x < g.count;
-                    const uint32_t pm = __ballot_sync(kFull, act);
-                    if (!pm) continue;
-                    n_qdist += __popc(pm);
-                    const float d = warp_distances<METRIC>(g, w, LeftSrc{w.q, 0}, x, act, staged);
-                    uint32_t cm = __ballot_sync(kFull, act && d < a_worst);
-                    while (cm) {
+            // All directed link updates of this level go through ONE add_link call site (the routine is large: three inlined
+            // copies made the kernel stall on instruction fetch). In order: the reverse links of this node's own links
+            // (reconnect_neighbor_nodes_), then — level 0 only — the peer pass: inserts that are in flight at the same time
+            // cannot find each other through the graph, so before this node leaves it measures its distance to every vector
+            // other warps are inserting right now and links both ways with those that are closer than its farthest own link
+            // and survive the heuristic against its kept links (same append / re-prune rule as any reverse link). With one
+            // insert in flight the registry is empty and the build stays byte-identical to the reference's single-thread build.
+            const bool peers = l == 0 && p.inflight && gridDim.x > 1;
+            uint32_t ri = 0, pbase = 0, cm = 0, px = kInvalid, xs = kInvalid;
+            float pd = 0.0f, dx = 0.0f;
+            bool second = false; // the slot <- xs half of a peer link is still to do
+            for (;;) {
+                uint32_t target, nbr;
+                float dtn;
+                int lvl = l;
+                bool count_dtn = false;
+                if (ri < nk) {
+                    const uint32_t close = mine_s[ri++];
+                    if (close == slot) continue;
+                    float dn = warp_distances<METRIC, MODE>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
+                    dn = __shfl_sync(kFull, dn, 0);
+                    target = close; nbr = slot; dtn = dn; count_dtn = true;
+                } else if (second) {
+                    target = slot; nbr = xs; dtn = dx; lvl = 0; second = false;
+                } else {
+                    if (!peers) break;
+                    bool found = false;
+                    while (!found) {
+                        if (!cm) { // next 32 registry entries
+                            if (pbase >= gridDim.x) break;
+                            const uint32_t wi = pbase + lane;
+                            pbase += 32;
+                            px = wi < gridDim.x ? __ldcg(p.inflight + wi) : kInvalid;
+                            const bool act = px != kInvalid && px != slot && px < g.count;
+                            const uint32_t pm = __ballot_sync(kFull, act);
+                            if (!pm) continue;
+                            n_qdist += __popc(pm);
+                            pd = warp_distances<METRIC, MODE>(g, w, LeftSrc{w.q, 0}, px, act, staged);
+                            cm = __ballot_sync(kFull, act && pd < a_worst);
+                            continue;
+                        }
                         const uint32_t j = __ffs(cm) - 1;
                         cm &= cm - 1;
-                        const uint32_t xs = __shfl_sync(kFull, x, j);
-                        const float dx = __shfl_sync(kFull, d, j);
+                        xs = __shfl_sync(kFull, px, j);
+                        dx = __shfl_sync(kFull, pd, j);
                         // the heuristic's own test for a candidate at distance dx: dropped if one of this node's links that
                         // is at least as close dominates it (refine_, index.hpp:3617-3627)
                         bool dominated = false;
@@ -304,14 +326,15 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
                             const uint32_t dm = __ballot_sync(kFull, a2);
                             if (!dm) continue;
                             w.n_pair += __popc(dm);
-                            const float dxs = warp_distances<METRIC>(g, w, LeftSrc{nullptr, xs}, a2 ? mine_s[b2 + lane] : kInvalid, a2, staged);
+                            const float dxs = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, xs}, a2 ? mine_s[b2 + lane] : kInvalid, a2, staged);
                             dominated |= __ballot_sync(kFull, a2 && dxs < dx) != 0u;
                         }
-                        if (dominated) continue;
-                        add_link<METRIC>(g, w, p.locks, xs, slot, dx, 0, kept_s, kept_d, top_limit_all, staged);
-                        add_link<METRIC>(g, w, p.locks, slot, xs, dx, 0, kept_s, kept_d, top_limit_all, staged);
+                        found = !dominated;
                     }
+                    if (!found) break;
+                    target = xs; nbr = slot; dtn = dx; lvl = 0; second = true;
                 }
+                add_link<METRIC, MODE>(g, w, p.locks, target, nbr, dtn, lvl, kept_s, kept_d, top_limit_all, staged, count_dtn);
             }
             t_recon += clock64() - t0;
         }
@@ -343,12 +366,17 @@ template <int METRIC> __global__ void __launch_bounds__(32) k_build(GraphView g,
     }
 }
 
-template <int METRIC> static cudaError_t launch_build_t(const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(k_build<METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
+template <int METRIC, int MODE> static cudaError_t launch_build_tm(const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(k_build<METRIC, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.sm.bytes);
     if (e != cudaSuccess) return e;
-    k_build<METRIC><<<grid, 32, p.sm.bytes, st>>>(g, p);
+    k_build<METRIC, MODE><<<grid, 32, p.sm.bytes, st>>>(g, p);
     count_launch();
     return cudaGetLastError();
+}
+template <int METRIC> static cudaError_t launch_build_t(const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t st) {
+    // every knob at its default (p.direct == 0, 32-row stage): the specialised kernel; GVSS_BUILD_GENERIC=1 forces MODE 0
+    static const bool generic = [] { const char *e = getenv("GVSS_BUILD_GENERIC"); return e && atoi(e); }();
+    return (p.direct == 0 && p.sm.stage_rows == 32 && !generic) ? launch_build_tm<METRIC, 3>(g, p, grid, st) : launch_build_tm<METRIC, 0>(g, p, grid, st);
 }
 
 cudaError_t launch_build(int metric, const GraphView &g, const BuildParams &p, uint32_t grid, cudaStream_t st) {

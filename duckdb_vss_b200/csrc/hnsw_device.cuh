@@ -385,6 +385,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
                                                 bool active, uint32_t &staged) {
     if (MODE == 1) return warp_distances_g4<METRIC, 1>(g, w, my_slot, active);
     if (MODE == 2) return warp_distances_g4<METRIC, 4>(g, w, my_slot, active); // latency kernel: 16 KB stage
+    const bool use_tma = MODE == 3 ? true : w.use_tma; // MODE 3: k_build's production configuration (1-D bulk copies, no A/B paths)
     const uint32_t lane = lane_id();
     const uint32_t chunk = w.chunk;
     const uint32_t nchunks = (g.dpad + chunk - 1) / chunk;
@@ -392,9 +393,9 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t rows = w.stage_rows;
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
-    if (w.g4 && left.smem == w.q) return warp_distances_g4<METRIC>(g, w, my_slot, active); // gather4 staging serves query-to-node distances only
+    if (MODE != 3 && w.g4 && left.smem == w.q) return warp_distances_g4<METRIC>(g, w, my_slot, active); // gather4 staging serves query-to-node distances only
 #if GVSS_DIRECT_PATH
-    if (w.direct && !stream_left) { // no staging at all: all 32 lanes at once
+    if (MODE != 3 && w.direct && !stream_left) { // no staging at all: all 32 lanes at once
         const float d = direct_distance<METRIC>(g.vectors, g.dpad, left.smem, my_slot, active);
         __syncwarp();
         return d;
@@ -418,7 +419,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
             const uint32_t ncopy = __popc(need_mask) + (stream_left ? 1u : 0u);
             if (ncopy == 0) return false;
             float *sbuf = buf ? w.stage[1] : w.stage[0];
-            if (w.use_tma) {
+            if (use_tma) {
                 uint64_t *bar = w.mbar + buf;
                 if (lane == 0) mbar_expect_tx(bar, ncopy * nfl * 4u);
                 __syncwarp();
@@ -459,7 +460,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
             bool pending_next = false;
             if (dbuf && ch + 1 < nchunks) pending_next = issue(ch + 1);
             if (pending) {
-                if (w.use_tma) {
+                if (use_tma) {
                     if (buf) { mbar_wait(w.mbar + 1, w.phase[1]); w.phase[1] ^= 1u; }
                     else { mbar_wait(w.mbar, w.phase[0]); w.phase[0] ^= 1u; }
                 } else {
@@ -790,7 +791,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                                             uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged, bool lq = false) {
     const uint32_t lane = lane_id();
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const bool cfg_g4 = MODE != 0 ? true : w.g4, cfg_pf_rows = MODE != 0 ? true : w.prefetch_rows,
+    const bool cfg_g4 = MODE == 3 ? false : (MODE != 0 ? true : w.g4), cfg_pf_rows = MODE == 3 ? false : (MODE != 0 ? true : w.prefetch_rows),
                cfg_pf_vis = MODE != 0 ? true : w.prefetch_vis, cfg_spec = MODE != 0 ? false : w.spec_prefetch;
     LeftSrc q{w.q, 0};
     uint32_t heap_size = 0, nvis = 1;
@@ -990,7 +991,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
         OPCLK(t_dist);
         OPC(kOpClkGather, t_dist - t_gather);
         // 2. their distances, stage_rows rows at a time (rows of the later batches are prefetched to L2 meanwhile)
-        const uint32_t bw = ((GVSS_DIRECT_PATH && MODE == 0 && w.direct) || cfg_g4) ? 32u : w.stage_rows; // rows per distance batch
+        const uint32_t bw = MODE == 3 ? 32u : (((GVSS_DIRECT_PATH && MODE == 0 && w.direct) || cfg_g4) ? 32u : w.stage_rows); // rows per distance batch
         if (cfg_g4 && cfg_pf_rows) {
             // gather4 staging takes one 128-byte line of every row per step: get ALL lines of all new rows moving towards L2
             // now, so that only the first step of the hop waits for DRAM
