@@ -390,7 +390,7 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
     const uint32_t chunk = w.chunk;
     const uint32_t nchunks = (g.dpad + chunk - 1) / chunk;
     const bool dbuf = w.nbuf == 2;
-    const uint32_t rows = w.stage_rows;
+    const uint32_t rows = MODE == 3 ? 32u : w.stage_rows; // MODE 3: lane <-> row, one pass
     const bool cacheable = nchunks == 1 && rows == 32;
     const bool stream_left = left.smem == nullptr;
     if (MODE != 3 && w.g4 && left.smem == w.q) return warp_distances_g4<METRIC>(g, w, my_slot, active); // gather4 staging serves query-to-node distances only
