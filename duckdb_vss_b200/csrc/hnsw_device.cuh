@@ -454,17 +454,26 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
             return true;
         };
 
-        bool pending = issue(0);
+        // chunk pipeline with ONE issue site (the routine is inlined at many places; k_build is large enough to stall on
+        // instruction fetch): chunk ch is awaited with chunk ch + 1 already in flight when the stage is double-buffered
+        uint32_t issued = 0;
+        bool pend0 = false, pend1 = false; // by chunk parity
+#pragma unroll 1
         for (uint32_t ch = 0; ch < nchunks; ch++) {
             const uint32_t buf = dbuf ? (ch & 1u) : 0u;
-            bool pending_next = false;
-            if (dbuf && ch + 1 < nchunks) pending_next = issue(ch + 1);
-            if (pending) {
+            const uint32_t upto = min(nchunks, ch + (dbuf ? 2u : 1u));
+#pragma unroll 1
+            while (issued < upto) {
+                const bool any = issue(issued);
+                if (issued & 1u) pend1 = any; else pend0 = any;
+                issued++;
+            }
+            if ((ch & 1u) ? pend1 : pend0) {
                 if (use_tma) {
                     if (buf) { mbar_wait(w.mbar + 1, w.phase[1]); w.phase[1] ^= 1u; }
                     else { mbar_wait(w.mbar, w.phase[0]); w.phase[0] ^= 1u; }
                 } else {
-                    if (pending_next) cp_async_wait<1>(); else cp_async_wait<0>();
+                    if (issued > ch + 1u && ((ch & 1u) ? pend0 : pend1)) cp_async_wait<1>(); else cp_async_wait<0>();
                     __syncwarp();
                 }
             }
@@ -476,8 +485,6 @@ __device__ __forceinline__ float warp_distances(const GraphView &g, WarpWs &w, L
                 acc_chunk<METRIC>(acc, a, b, (int)(nfl / 4));
             }
             __syncwarp(); // all lanes are done reading this buffer before it is refilled
-            if (!dbuf && ch + 1 < nchunks) pending_next = issue(ch + 1);
-            pending = pending_next;
         }
         if (act) {
             staged = cacheable ? my_slot : kInvalid;
