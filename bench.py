@@ -246,6 +246,8 @@ def main():
     ap.add_argument("--nq", type=int, default=0, help="queries per step; 0 = the config's batch (10 000; join10m: 100 000)")
     ap.add_argument("--ef", type=int, default=0, help="0 = smallest ef of the sweep with recall@10 >= 0.95")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--M", type=int, default=0, help="connectivity (0 = the bench default 32; M0 = 2M)")
+    ap.add_argument("--efc", type=int, default=0, help="ef_construction (0 = the bench default 200)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "gvss" else args.warmup
     if args.impl == "reference":
@@ -269,6 +271,11 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     label, metric, d, n_default, gen = WORKLOADS[args.workload]
+    global M_BENCH, M0_BENCH, EFC_BENCH
+    if args.M:
+        M_BENCH, M0_BENCH = args.M, 2 * args.M
+    if args.efc:
+        EFC_BENCH = args.efc
     strong = args.workload != "sift1m"     # ONE named set, partitioned over the ranks when there are several
     nq, k, M, M0 = args.nq or DEFAULT_NQ.get(args.workload, 10_000), 10, M_BENCH, M0_BENCH
     ef_sweep = EF_SWEEP_WIDE if args.workload == "join10m" else EF_SWEEP

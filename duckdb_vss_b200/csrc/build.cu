@@ -123,52 +123,6 @@ __device__ __forceinline__ uint32_t refine(const GraphView &g, WarpWs &w, uint32
     return nkept;
 }
 
-// One directed link update under the target's lock: append `nbr` to `target`'s list on `level`, or, when the list is
-// full, re-run the heuristic over {(d_tn, nbr)} ∪ {(d(target, x), x)} with needed = capacity
-// (reconnect_neighbor_nodes_, index.hpp:3279-3311). `d_tn` = d(target, nbr).
-template <int METRIC, int MODE>
-__device__ __forceinline__ void add_link(const GraphView &g, WarpWs &w, uint32_t *locks, uint32_t target, uint32_t nbr, float d_tn,
-                                         int level, uint32_t *kept_s, float *kept_d, uint32_t top_limit_all, uint32_t &staged,
-                                         bool count_d_tn = false) {
-    const uint32_t lane = lane_id();
-    uint32_t capc;
-    uint32_t *clist = list_ptr(g, target, level, capc);
-    lock_node(locks, target);
-    uint32_t cntc = 0;
-    bool present = false;
-    for (uint32_t base = 0; base < capc; base += 32) {
-        const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
-        cntc += __popc(__ballot_sync(kFull, e != kInvalid));
-        present |= __ballot_sync(kFull, e == nbr) != 0;
-    }
-    if (present) { unlock_node(locks, target); return; }
-    if (cntc < capc) {
-        if (lane == 0) clist[cntc] = nbr;
-        w.n_rows_written++;
-        unlock_node(locks, target);
-        return;
-    }
-    uint32_t tsz = 0;
-    if (count_d_tn) w.n_qdist++; // the reference measures d(target, new node) only here, when the list has to be re-pruned
-    top_insert(w, tsz, top_limit_all, d_tn, nbr);
-    for (uint32_t base = 0; base < capc; base += 32) {
-        const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
-        const bool act = e != kInvalid;
-        const uint32_t am = __ballot_sync(kFull, act);
-        if (!am) break;
-        w.n_pair += __popc(am);
-        const float d = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, target}, e, act, staged);
-        for (uint32_t m = am; m; m &= m - 1) {
-            const uint32_t j = __ffs(m) - 1;
-            top_insert(w, tsz, top_limit_all, __shfl_sync(kFull, d, j), __shfl_sync(kFull, e, j));
-        }
-    }
-    const uint32_t nk2 = refine<METRIC, MODE>(g, w, tsz, capc, kept_s, kept_d, staged);
-    for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
-    w.n_rows_written++;
-    unlock_node(locks, target);
-}
-
 // MODE 3 = the production configuration fixed at compile time (32-row stage, TMA bulk copies, prefetches as shipped): the A/B
 // paths stay out of the kernel, which is otherwise large enough to stall on instruction fetch; MODE 0 = run-time knobs.
 template <int METRIC, int MODE> __global__ void __launch_bounds__(32) k_build(GraphView g, BuildParams p) {
@@ -242,99 +196,146 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32) k_build(Gr
             for (uint32_t i = lane; i < top_size; i += 32) w.top_s[i] &= kSlotMask; // drop the expanded flags
             __syncwarp();
 
-            // connect_new_node_: up to M links on every level (clamped to the list size when M0 < M)
-            const uint32_t cap_l = l ? g.M : g.M0;
+            // Everything that follows on this level — the node's own list (connect_new_node_), the reverse links of its links
+            // (reconnect_neighbor_nodes_) and, on level 0, the peer pass — is ONE loop with ONE refine site and one list-rewrite
+            // site: the routines are large and every further inlined copy made the kernel stall on instruction fetch
+            // (profiles/r3_build_ncu_summary.txt). Order of the link updates: own list; reverse links in list order; then the
+            // peers. Peer pass: inserts that are in flight at the same time cannot find each other through the graph, so before
+            // this node leaves it measures its distance to every vector other warps are inserting right now and links both ways
+            // with those that are closer than its farthest own link and survive the heuristic against its kept links (same
+            // append / re-prune rule as any reverse link). With one insert in flight the registry is empty and the build stays
+            // byte-identical to the reference's single-thread build.
+            const uint32_t cap_l = l ? g.M : g.M0; // own links: up to M on every level, clamped to the list size when M0 < M
             t_beam += clock64() - t0; t0 = clock64();
-            uint32_t nk = refine<METRIC, MODE>(g, w, top_size, g.M, kept_s, kept_d, staged);
-            nk = min(nk, cap_l);
-            t_refine += clock64() - t0; t0 = clock64();
-            for (uint32_t i = lane; i < nk; i += 32) { mine_s[i] = kept_s[i]; mine_d[i] = kept_d[i]; }
-            __syncwarp();
-            uint32_t capx;
-            uint32_t *mylist = list_ptr(g, slot, l, capx);
-            lock_node(p.locks, slot);
-            {
-                // the list is normally blank; links appended meanwhile by concurrent inserts are kept behind ours
-                uint32_t extra = kInvalid;
-                if (lane < capx) extra = __ldcg(mylist + lane);
-                bool keep_extra = extra != kInvalid;
-                for (uint32_t i = 0; i < nk; i++) if (extra == mine_s[i]) keep_extra = false;
-                const uint32_t emask = __ballot_sync(kFull, keep_extra);
-                const uint32_t epos = nk + __popc(emask & ((1u << lane) - 1u));
-                __syncwarp();
-                for (uint32_t i = lane; i < capx; i += 32) mylist[i] = i < nk ? mine_s[i] : kInvalid;
-                __syncwarp();
-                if (keep_extra && epos < capx) mylist[epos] = extra;
-            }
-            unlock_node(p.locks, slot);
-            w.n_rows_written++;
-            closest = mine_s[0];
-            t_conn += clock64() - t0; t0 = clock64();
-
-            // reconnect_neighbor_nodes_
-            const float a_worst = nk ? kept_d[nk - 1] : CUDART_INF_F; // distance of this node's farthest own link
-            // All directed link updates of this level go through ONE add_link call site (the routine is large: three inlined
-            // copies made the kernel stall on instruction fetch). In order: the reverse links of this node's own links
-            // (reconnect_neighbor_nodes_), then — level 0 only — the peer pass: inserts that are in flight at the same time
-            // cannot find each other through the graph, so before this node leaves it measures its distance to every vector
-            // other warps are inserting right now and links both ways with those that are closer than its farthest own link
-            // and survive the heuristic against its kept links (same append / re-prune rule as any reverse link). With one
-            // insert in flight the registry is empty and the build stays byte-identical to the reference's single-thread build.
             const bool peers = l == 0 && p.inflight && gridDim.x > 1;
-            uint32_t ri = 0, pbase = 0, cm = 0, px = kInvalid, xs = kInvalid;
-            float pd = 0.0f, dx = 0.0f;
-            bool second = false; // the slot <- xs half of a peer link is still to do
+            bool own_done = false, second = false; // second: the slot <- xs half of a peer link is still to do
+            uint32_t nk = 0, ri = 0, pbase = 0, cm = 0, px = kInvalid, xs = kInvalid;
+            float a_worst = CUDART_INF_F, pd = 0.0f, dx = 0.0f;
             for (;;) {
-                uint32_t target, nbr;
-                float dtn;
-                int lvl = l;
-                bool count_dtn = false;
-                if (ri < nk) {
-                    const uint32_t close = mine_s[ri++];
-                    if (close == slot) continue;
-                    float dn = warp_distances<METRIC, MODE>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
-                    dn = __shfl_sync(kFull, dn, 0);
-                    target = close; nbr = slot; dtn = dn; count_dtn = true;
-                } else if (second) {
-                    target = slot; nbr = xs; dtn = dx; lvl = 0; second = false;
+                uint32_t target = slot, ncand, needed, capc = 0;
+                uint32_t *clist = nullptr;
+                if (!own_done) {
+                    ncand = top_size; needed = g.M; // candidates = the beam search's result list
                 } else {
-                    if (!peers) break;
-                    bool found = false;
-                    while (!found) {
-                        if (!cm) { // next 32 registry entries
-                            if (pbase >= gridDim.x) break;
-                            const uint32_t wi = pbase + lane;
-                            pbase += 32;
-                            px = wi < gridDim.x ? __ldcg(p.inflight + wi) : kInvalid;
-                            const bool act = px != kInvalid && px != slot && px < g.count;
-                            const uint32_t pm = __ballot_sync(kFull, act);
-                            if (!pm) continue;
-                            n_qdist += __popc(pm);
-                            pd = warp_distances<METRIC, MODE>(g, w, LeftSrc{w.q, 0}, px, act, staged);
-                            cm = __ballot_sync(kFull, act && pd < a_worst);
-                            continue;
+                    uint32_t nbr;
+                    float dtn;
+                    int lvl = l;
+                    bool count_dtn = false;
+                    if (ri < nk) {
+                        const uint32_t close = mine_s[ri++];
+                        if (close == slot) continue;
+                        float dn = warp_distances<METRIC, MODE>(g, w, LeftSrc{w.q, 0}, close, lane == 0, staged);
+                        dn = __shfl_sync(kFull, dn, 0);
+                        target = close; nbr = slot; dtn = dn; count_dtn = true;
+                    } else if (second) {
+                        target = slot; nbr = xs; dtn = dx; lvl = 0; second = false;
+                    } else {
+                        if (!peers) break;
+                        bool found = false;
+                        while (!found) {
+                            if (!cm) { // next 32 registry entries
+                                if (pbase >= gridDim.x) break;
+                                const uint32_t wi = pbase + lane;
+                                pbase += 32;
+                                px = wi < gridDim.x ? __ldcg(p.inflight + wi) : kInvalid;
+                                const bool act = px != kInvalid && px != slot && px < g.count;
+                                const uint32_t pm = __ballot_sync(kFull, act);
+                                if (!pm) continue;
+                                n_qdist += __popc(pm);
+                                pd = warp_distances<METRIC, MODE>(g, w, LeftSrc{w.q, 0}, px, act, staged);
+                                cm = __ballot_sync(kFull, act && pd < a_worst);
+                                continue;
+                            }
+                            const uint32_t j = __ffs(cm) - 1;
+                            cm &= cm - 1;
+                            xs = __shfl_sync(kFull, px, j);
+                            dx = __shfl_sync(kFull, pd, j);
+                            // the heuristic's own test for a candidate at distance dx: dropped if one of this node's links that
+                            // is at least as close dominates it (refine_, index.hpp:3617-3627)
+                            bool dominated = false;
+                            for (uint32_t b2 = 0; b2 < nk; b2 += 32) {
+                                const bool a2 = b2 + lane < nk && mine_d[b2 + lane] <= dx;
+                                const uint32_t dm = __ballot_sync(kFull, a2);
+                                if (!dm) continue;
+                                w.n_pair += __popc(dm);
+                                const float dxs = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, xs}, a2 ? mine_s[b2 + lane] : kInvalid, a2, staged);
+                                dominated |= __ballot_sync(kFull, a2 && dxs < dx) != 0u;
+                            }
+                            found = !dominated;
                         }
-                        const uint32_t j = __ffs(cm) - 1;
-                        cm &= cm - 1;
-                        xs = __shfl_sync(kFull, px, j);
-                        dx = __shfl_sync(kFull, pd, j);
-                        // the heuristic's own test for a candidate at distance dx: dropped if one of this node's links that
-                        // is at least as close dominates it (refine_, index.hpp:3617-3627)
-                        bool dominated = false;
-                        for (uint32_t b2 = 0; b2 < nk; b2 += 32) {
-                            const bool a2 = b2 + lane < nk && mine_d[b2 + lane] <= dx;
-                            const uint32_t dm = __ballot_sync(kFull, a2);
-                            if (!dm) continue;
-                            w.n_pair += __popc(dm);
-                            const float dxs = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, xs}, a2 ? mine_s[b2 + lane] : kInvalid, a2, staged);
-                            dominated |= __ballot_sync(kFull, a2 && dxs < dx) != 0u;
-                        }
-                        found = !dominated;
+                        if (!found) break;
+                        target = xs; nbr = slot; dtn = dx; lvl = 0; second = true;
                     }
-                    if (!found) break;
-                    target = xs; nbr = slot; dtn = dx; lvl = 0; second = true;
+                    // one directed link update under the target's lock: append `nbr` to `target`'s list, or, when the list is
+                    // full, re-run the heuristic over {(dtn, nbr)} U {(d(target, x), x)} with needed = capacity
+                    // (reconnect_neighbor_nodes_, index.hpp:3279-3311)
+                    clist = list_ptr(g, target, lvl, capc);
+                    lock_node(p.locks, target);
+                    uint32_t cntc = 0;
+                    bool present = false;
+                    for (uint32_t base = 0; base < capc; base += 32) {
+                        const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
+                        cntc += __popc(__ballot_sync(kFull, e != kInvalid));
+                        present |= __ballot_sync(kFull, e == nbr) != 0;
+                    }
+                    if (present) { unlock_node(p.locks, target); continue; }
+                    if (cntc < capc) {
+                        if (lane == 0) clist[cntc] = nbr;
+                        w.n_rows_written++;
+                        unlock_node(p.locks, target);
+                        continue;
+                    }
+                    uint32_t tsz = 0;
+                    if (count_dtn) w.n_qdist++; // the reference measures d(target, new node) only here, when the list has to be re-pruned
+                    top_insert(w, tsz, top_limit_all, dtn, nbr);
+                    for (uint32_t base = 0; base < capc; base += 32) {
+                        const uint32_t e = base + lane < capc ? __ldcg(clist + base + lane) : kInvalid;
+                        const bool act = e != kInvalid;
+                        const uint32_t am = __ballot_sync(kFull, act);
+                        if (!am) break;
+                        w.n_pair += __popc(am);
+                        const float d = warp_distances<METRIC, MODE>(g, w, LeftSrc{nullptr, target}, e, act, staged);
+                        for (uint32_t m = am; m; m &= m - 1) {
+                            const uint32_t j = __ffs(m) - 1;
+                            top_insert(w, tsz, top_limit_all, __shfl_sync(kFull, d, j), __shfl_sync(kFull, e, j));
+                        }
+                    }
+                    ncand = tsz; needed = capc;
                 }
-                add_link<METRIC, MODE>(g, w, p.locks, target, nbr, dtn, lvl, kept_s, kept_d, top_limit_all, staged, count_dtn);
+                const uint32_t nk2 = refine<METRIC, MODE>(g, w, ncand, needed, kept_s, kept_d, staged); // the single site
+                if (own_done) {
+                    for (uint32_t j = lane; j < capc; j += 32) clist[j] = j < nk2 ? kept_s[j] : kInvalid;
+                    w.n_rows_written++;
+                    unlock_node(p.locks, target);
+                    continue;
+                }
+                // connect_new_node_ (index.hpp:3247-3267)
+                nk = min(nk2, cap_l);
+                t_refine += clock64() - t0; t0 = clock64();
+                for (uint32_t i = lane; i < nk; i += 32) { mine_s[i] = kept_s[i]; mine_d[i] = kept_d[i]; }
+                __syncwarp();
+                uint32_t capx;
+                uint32_t *mylist = list_ptr(g, slot, l, capx);
+                lock_node(p.locks, slot);
+                {
+                    // the list is normally blank; links appended meanwhile by concurrent inserts are kept behind ours
+                    uint32_t extra = kInvalid;
+                    if (lane < capx) extra = __ldcg(mylist + lane);
+                    bool keep_extra = extra != kInvalid;
+                    for (uint32_t i = 0; i < nk; i++) if (extra == mine_s[i]) keep_extra = false;
+                    const uint32_t emask = __ballot_sync(kFull, keep_extra);
+                    const uint32_t epos = nk + __popc(emask & ((1u << lane) - 1u));
+                    __syncwarp();
+                    for (uint32_t i = lane; i < capx; i += 32) mylist[i] = i < nk ? mine_s[i] : kInvalid;
+                    __syncwarp();
+                    if (keep_extra && epos < capx) mylist[epos] = extra;
+                }
+                unlock_node(p.locks, slot);
+                w.n_rows_written++;
+                closest = mine_s[0];
+                a_worst = nk ? kept_d[nk - 1] : CUDART_INF_F; // distance of this node's farthest own link
+                own_done = true;
+                t_conn += clock64() - t0; t0 = clock64();
             }
             t_recon += clock64() - t0;
         }
