@@ -173,7 +173,8 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32) k_build(Gr
         w.n_rows_written = 0;
         uint32_t n_qdist = 0, n_base = 0;
         long long t0 = clock64(), t_beam = 0, t_refine = 0, t_conn = 0, t_recon = 0;
-        uint32_t closest = greedy_descent<METRIC, true, MODE>(g, w, entry, max_level, level, cnt, staged);
+        float closest_d;
+        uint32_t closest = greedy_descent<METRIC, true, MODE>(g, w, entry, max_level, level, cnt, staged, closest_d);
         const long long t_greedy = clock64() - t0;
 
         for (int l = min(level, max_level); l >= 0; --l) {
@@ -186,7 +187,7 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32) k_build(Gr
             for (;;) {
                 cnt.flags = 0;
                 w.use_bitmap = bitmap;
-                beam_search<METRIC, true, true, MODE>(g, w, closest, p.ef_add, l, slot, cnt, top_size, staged, lq);
+                beam_search<METRIC, true, true, MODE>(g, w, closest, closest_d, p.ef_add, l, slot, cnt, top_size, staged, lq);
                 if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
                 if (cnt.flags & 8u) { lq = false; continue; }
                 break;
@@ -332,7 +333,7 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32) k_build(Gr
                 }
                 unlock_node(p.locks, slot);
                 w.n_rows_written++;
-                closest = mine_s[0];
+                if (nk) { closest = mine_s[0]; closest_d = mine_d[0]; } // the next level starts at this level's best link
                 a_worst = nk ? kept_d[nk - 1] : CUDART_INF_F; // distance of this node's farthest own link
                 own_done = true;
                 t_conn += clock64() - t0; t0 = clock64();

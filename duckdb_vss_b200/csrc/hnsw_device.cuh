@@ -709,7 +709,7 @@ __device__ __forceinline__ uint32_t *list_ptr(const GraphView &g, uint32_t slot,
 // search_for_one_ (index.hpp:3384-3422): greedy descent from `closest` through levels begin..end+1.
 template <int METRIC, bool VOLATILE, int MODE = 0>
 __device__ __forceinline__ uint32_t greedy_descent(const GraphView &g, WarpWs &w, uint32_t closest, int begin_level,
-                                                   int end_level, Counters &cnt, uint32_t &staged) {
+                                                   int end_level, Counters &cnt, uint32_t &staged, float &closest_d) {
     const uint32_t lane = lane_id();
     LeftSrc q{w.q, 0};
     float cd = warp_distances<METRIC, MODE>(g, w, q, closest, lane == 0, staged);
@@ -751,6 +751,7 @@ __device__ __forceinline__ uint32_t greedy_descent(const GraphView &g, WarpWs &w
             cnt.cycles++;
         } while (changed);
     }
+    closest_d = cd; // d(query, closest): the beam search that starts there need not fetch the row again
     return closest;
 }
 
@@ -794,7 +795,9 @@ constexpr uint32_t kExpanded = 0x80000000u;
 constexpr uint32_t kSlotMask = 0x7FFFFFFFu;
 
 template <int METRIC, bool INSERT, bool VOLATILE, int MODE = 0>
-__device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, uint32_t limit, int level,
+// start_d = d(query, start), already known to the caller (greedy descent, or the previous level's best link): the reference
+// evaluates it again here (counted below), the bits are the same.
+__device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint32_t start, float start_d, uint32_t limit, int level,
                                             uint32_t new_slot, Counters &cnt, uint32_t &top_size, uint32_t &staged, bool lq = false) {
     const uint32_t lane = lane_id();
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -836,8 +839,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
     top_size = 0;
     vis_clear(w);
 
-    float radius = warp_distances<METRIC, MODE>(g, w, q, start, lane == 0, staged);
-    radius = __shfl_sync(kFull, radius, 0);
+    float radius = start_d;
     if (radius != radius) radius = CUDART_INF_F;
     cnt.computed++;
     if (!lq) heap_push(w, heap_size, radius, start);
@@ -875,7 +877,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
             }
             // removed members (search only): the reference keeps them in its queue but not in the list. Here they wait in a
             // min-heap of their own (the heap_* storage) and are expanded when they are closer than every live candidate.
-            const bool have_t = heap_size != 0;
+            const bool have_t = !INSERT && heap_size != 0; // (an insert-time search lists every member: nothing ever waits there)
             const Cand tm = have_t ? heap_get(w, 0) : Cand{CUDART_INF_F, kInvalid};
             bool tie, take_t = false;
             if (cur >= top_size) {
@@ -1068,7 +1070,7 @@ __device__ __forceinline__ void beam_search(const GraphView &g, WarpWs &w, uint3
                 if (acc && at < log_cap) log_put(at, dj, sj);
                 logn += __popc(accmask);
                 log_ok = log_ok && logn <= log_cap;
-                for (uint32_t m = accmask & ~amask; m; m &= m - 1) {
+                for (uint32_t m = INSERT ? 0u : (accmask & ~amask); m; m &= m - 1) {
                     const uint32_t i = __ffs(m) - 1;
                     if (!heap_push(w, heap_size, __shfl_sync(kFull, dj, i), __shfl_sync(kFull, sj, i))) cnt.flags |= 1u;
                 }

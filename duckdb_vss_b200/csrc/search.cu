@@ -78,13 +78,15 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32, MODE == 2 
         for (int i = 0; i < kOpCount; i++) w.opc[i] = i == kOpQueries ? 1ull : 0ull;
 #endif
         if (p.cluster_out) { // compact (index.hpp:3043-3046): only the node the descent through levels max_level..1 ends at
-            const uint32_t closest = greedy_descent<METRIC, false, MODE>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            float closest_d;
+            const uint32_t closest = greedy_descent<METRIC, false, MODE>(g, w, p.entry, p.max_level, 0, cnt, staged, closest_d);
             if (lane == 0) p.cluster_out[qi] = closest;
             __syncwarp();
             continue;
         }
         if (g.count && p.k) {
-            const uint32_t closest = greedy_descent<METRIC, false, MODE>(g, w, p.entry, p.max_level, 0, cnt, staged);
+            float closest_d;
+            const uint32_t closest = greedy_descent<METRIC, false, MODE>(g, w, p.entry, p.max_level, 0, cnt, staged, closest_d);
             const Counters before = cnt;
             // list-as-queue first (hashed visited table); a query that would overfill the table is redone with the exact
             // bitmap (flag bit1); exact ties switch to usearch's heap mid-flight (flag bit2), or — if the operation log ran
@@ -95,7 +97,7 @@ template <int METRIC, int MODE> __global__ void __launch_bounds__(32, MODE == 2 
             for (;;) {
                 cnt = before;
                 w.use_bitmap = bitmap;
-                beam_search<METRIC, false, false, MODE>(g, w, closest, p.limit, 0, kInvalid, cnt, top_size, staged, lq);
+                beam_search<METRIC, false, false, MODE>(g, w, closest, closest_d, p.limit, 0, kInvalid, cnt, top_size, staged, lq);
                 if ((cnt.flags & 1u) && !bitmap) { bitmap = true; continue; }
                 if (cnt.flags & 8u) { lq = false; continue; }
                 break;
