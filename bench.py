@@ -41,7 +41,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "hnsw_search_qps_at_recall10_ge_0.95"
-EF_SWEEP = (16, 32, 64, 96, 128, 160, 192, 224, 256, 288, 320, 384, 512)
+EF_SWEEP = (16, 32, 64, 96, 128, 160, 192, 224, 256, 288, 304, 320, 384, 512)
 # with the usearch defaults (M=16, efc=128) recall@10 >= 0.95 is NOT reachable on the 1M set within
 # ef <= 512 (reference-built graph: 0.80 at ef=512, profiles/recall_1m_r1.txt), so both arms use M=32 / ef_construction=200.
 M_BENCH, M0_BENCH, EFC_BENCH = 32, 64, 200

@@ -71,3 +71,25 @@ def test_persistence_round_trip_through_callbacks_is_pipelined_and_exact(tmp_pat
     print(out)
     m = re.search(r"stream_bytes (\d+) serialized_length (\d+) save_s ([0-9.]+) .* load_s ([0-9.]+) .* same_results 1", out)
     assert m and m.group(1) == m.group(2), out
+
+
+def test_concurrent_single_query_scans_keep_up_with_the_reference_threads(tmp_path):
+    """T host threads each issue one query per call (concurrent HNSW_INDEX_SCANs); the calls overlap on the GPU (a search slot
+    each) and together keep up with the compiled reference searching the same graph with T threads; ids identical."""
+    import oracle
+    exe = str(tmp_path / "scan_driver")
+    libdir = os.path.dirname(capi.LIB_PATH)
+    subprocess.run(["g++", "-std=c++17", "-O2", "-pthread", f"-I{ROOT}/include", f"{ROOT}/tests/cpp/scan_driver.cpp", f"-L{libdir}", "-lgvss",
+                    "-ldl", f"-Wl,-rpath,{libdir}", "-o", exe], check=True)
+    ref = oracle.REF_SO if oracle.have_ref() else "-"
+    T = min(16, os.cpu_count() or 4)
+    out = subprocess.run([exe, "200000", "128", "32", "128", str(T), ref], check=True, capture_output=True, text=True, timeout=900).stdout
+    print(out)
+    m = re.search(r"gvss single_query_median_ms ([0-9.]+) p95_ms [0-9.]+ threads_qps ([0-9.]+) failures 0 concurrent_peak (\d+)", out)
+    assert m, out
+    assert int(m.group(3)) >= 2, out
+    r = re.search(r"reference single_query_mean_ms ([0-9.]+) threads_qps ([0-9.]+) same_ids (\d)", out)
+    if r:
+        assert r.group(3) == "1", out
+        assert float(m.group(2)) >= 0.8 * float(r.group(2)), out     # T threads of single queries keep up with T reference threads
+        assert float(m.group(1)) <= 1.1 * float(r.group(1)), out     # and one query is no slower than one reference thread
