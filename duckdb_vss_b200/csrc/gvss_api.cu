@@ -127,7 +127,8 @@ struct gvss_index {
         std::vector<int64_t> keys;
     };
     uint32_t host_threads = 1;
-    std::vector<std::unique_ptr<Stage>> stages; // [host_threads + 1]; the last one belongs to GVSS_ANY_THREAD
+    std::vector<std::unique_ptr<Stage>> stages; // [host_threads + kAnyStages]; the last kAnyStages belong to GVSS_ANY_THREAD callers
+    static constexpr size_t kAnyStages = 8;     // (picked by a hash of the calling thread: concurrent INSERT / Sink threads do not queue on one mutex)
     std::vector<std::pair<const float *, std::vector<int64_t>>> st_device; // rows already on the device (guarded by rw, exclusive)
     std::atomic<uint64_t> staged{0};
     std::atomic<int64_t> room{0}; // rows that may still be added: capacity + free slots - nodes - staged (index.hpp:2329-2335)
@@ -558,7 +559,7 @@ int gvss_create(const gvss_config *config, gvss_index **out) {
         if (x->stream) cudaStreamDestroy(x->stream);
         return fail("gvss_create: CUDA initialisation failed: %s", why);
     }
-    for (int i = 0; i < 2; i++) x->stages.push_back(std::make_unique<gvss_index::Stage>()); // thread 0 + GVSS_ANY_THREAD
+    for (size_t i = 0; i < 1 + gvss_index::kAnyStages; i++) x->stages.push_back(std::make_unique<gvss_index::Stage>()); // thread 0 + GVSS_ANY_THREAD
     *out = x.release();
     return 0;
     API_END
@@ -682,10 +683,10 @@ int gvss_reserve(gvss_index *x, uint64_t members, uint32_t host_threads) {
     if (host_threads > 65536) return fail("gvss_reserve: %u host threads", host_threads);
     if (host_threads > x->host_threads) {
         // thread ids 0..host_threads-1 become valid; the GVSS_ANY_THREAD buffer stays last
-        auto any = std::move(x->stages.back());
-        x->stages.pop_back();
+        std::vector<std::unique_ptr<gvss_index::Stage>> any; // the GVSS_ANY_THREAD buffers stay last
+        for (size_t i = 0; i < gvss_index::kAnyStages; i++) { any.push_back(std::move(x->stages.back())); x->stages.pop_back(); }
         while (x->stages.size() < host_threads) x->stages.push_back(std::make_unique<gvss_index::Stage>());
-        x->stages.push_back(std::move(any));
+        while (!any.empty()) { x->stages.push_back(std::move(any.back())); any.pop_back(); }
         x->host_threads = host_threads;
     }
     x->level_rng = 1; // reserve() allocates fresh thread contexts => the level sequence restarts (index.hpp:2113,2124)
@@ -700,7 +701,7 @@ int gvss_add(gvss_index *x, int64_t key, const float *vec, uint32_t host_thread)
     if (x->router) return router_add(x->router, key, vec, host_thread);
     if (!x->poisoned.empty()) return check_usable(x);
     size_t t;
-    if (host_thread == GVSS_ANY_THREAD) t = x->stages.size() - 1;
+    if (host_thread == GVSS_ANY_THREAD) t = x->stages.size() - gvss_index::kAnyStages + std::hash<std::thread::id>()(std::this_thread::get_id()) % gvss_index::kAnyStages;
     else if (host_thread < x->host_threads) t = host_thread;
     else return fail("gvss_add: thread id %u is not below the %u reserved by gvss_reserve (or GVSS_ANY_THREAD)", host_thread, x->host_threads);
     // capacity check as usearch: nodes_count_.fetch_add(1) >= capacity fails (index.hpp:2329-2335); removed slots are reusable
