@@ -460,7 +460,6 @@ def main():
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    l0 = gv.lib().gvss_kernel_launches()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     # keep the GPUs under the same load until every rank's sampler delivers (all ranks take the same number of extra steps: the
@@ -478,6 +477,7 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     clocks.rows.clear()
+    l0 = gv.lib().gvss_kernel_launches()
     t_wall0 = time.perf_counter()
     t_begin.record(s_search)
     for a, b in ev:
