@@ -64,3 +64,23 @@ def test_shard_ranges_cover_everything():
         r = [sharded.shard_range(n, i, w) for i in range(w)]
         assert r[0][0] == 0 and r[-1][1] == n and all(r[i][1] == r[i + 1][0] for i in range(w - 1))
         assert max(e - b for b, e in r) - min(e - b for b, e in r) <= 1
+
+
+def test_weak_scaling_shards_are_samples_of_one_data_set():
+    """bench.py's weak-scaling shards: rank 0 holds exactly the N=1 set; the other ranks hold other samples of the SAME data set
+    (same cluster centres and projection, other points), so the queries are in-distribution for every shard."""
+    import numpy as np
+    from duckdb_vss_b200 import synth
+    n, d, C = 4000, 16, 40
+    base0, q = synth.clustered(n, d, C, 4, 42, 50)
+    again, _ = synth.clustered(n, d, C, 4, 42, 0, point_seed=None)
+    other, _ = synth.clustered(n, d, C, 4, 42, 0, point_seed=1042)
+    alien, _ = synth.clustered(n, d, C, 4, 1042, 0)
+    assert np.array_equal(base0, again) and not np.array_equal(base0, other)
+
+    def nearest(x, y):  # mean distance from each row of x to its nearest row of y
+        d2 = ((x[:, None, :] - y[None, :, :]) ** 2).sum(-1)
+        return float(np.sqrt(d2.min(1)).mean())
+    # queries of the seed-42 set find close rows in another sample of the same set, not in an unrelated set
+    assert nearest(q, other) < 0.6 * nearest(q, alien)
+    assert abs(nearest(q, other) - nearest(q, base0)) < 0.25 * nearest(q, base0)
