@@ -132,6 +132,10 @@ struct gvss_index {
     std::vector<std::pair<const float *, std::vector<int64_t>>> st_device; // rows already on the device (guarded by rw, exclusive)
     std::atomic<uint64_t> staged{0};
     std::atomic<int64_t> room{0}; // rows that may still be added: capacity + free slots - nodes - staged (index.hpp:2329-2335)
+    // what gvss_get_info reports, republished by every writer before it lets go of `rw`: size() / capacity() are asked for by
+    // HNSWIndex::Construct before every chunk (hnsw_index.cpp:413-431) and must not wait for a flush that holds the writer lock
+    std::atomic<uint64_t> pub_capacity{0}, pub_count{0}, pub_deleted{0}, pub_upper_cap{0}, pub_scratch{0};
+    std::atomic<int32_t> pub_max_level{-1};
 
     // Locking. `rw` plays the role usearch's per-node locks and per-thread contexts play in the reference: searches hold it
     // shared and run concurrently, everything that changes the graph holds it exclusively. `dev_mu` orders the enqueue
@@ -176,6 +180,15 @@ static void free_device(gvss_index *x) {
 static void recompute_room(gvss_index *x) {
     x->room = (int64_t)x->capacity + (int64_t)x->free_slots.size() - (int64_t)x->count - (int64_t)x->staged.load();
 }
+
+static void publish_info(gvss_index *x) {
+    x->pub_capacity = x->capacity; x->pub_count = x->count; x->pub_deleted = x->n_deleted; x->pub_upper_cap = x->upper_cap;
+    x->pub_scratch = x->scratch_bytes; x->pub_max_level = x->max_level;
+}
+struct Publish { // declared right after a writer lock: runs before the lock is released
+    gvss_index *x;
+    ~Publish() { publish_info(x); }
+};
 
 static int ensure_capacity(gvss_index *x, uint64_t members) {
     if (members <= x->capacity) return 0;
@@ -443,6 +456,7 @@ static int check_usable(const gvss_index *x) {
 static int flush_if_staged(gvss_index *x) {
     if (!x->staged.load()) return 0;
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     return flush_locked(x);
 }
 
@@ -485,6 +499,7 @@ static void background_builder(gvss_index *x) {
             if (x->bg_stop) return;
         }
         std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
         if (!x->poisoned.empty()) { x->bg_min_rows = 0; continue; } // nothing more to do for a broken index: go back to sleep
         if (!x->bg_min_rows.load() || x->staged.load() < x->bg_min_rows.load()) continue;
         if (flush_locked(x)) {
@@ -608,6 +623,7 @@ int gvss_reset(gvss_index *x) {
     if (!x) return fail("null index");
     if (x->router) return router_reset(x->router);
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     reset_locked(x);
     return 0;
@@ -628,6 +644,7 @@ int gvss_compact_rebuild(gvss_index *x, uint64_t *dropped) {
     if (check_usable(x)) return 1;
     if (x->router) return router_compact(x->router, true, dropped);
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     if (flush_locked(x)) return 1;
     wait_device_searches(x);
@@ -678,6 +695,7 @@ int gvss_reserve(gvss_index *x, uint64_t members, uint32_t host_threads) {
     if (check_usable(x)) return 1;
     if (x->router) return router_reserve(x->router, members, host_threads);
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     if (host_threads == 0) host_threads = 1;
     if (host_threads > 65536) return fail("gvss_reserve: %u host threads", host_threads);
@@ -750,6 +768,7 @@ int gvss_add_batch_device(gvss_index *x, const int64_t *keys_host, const float *
     if (check_usable(x)) return 1;
     if (x->router) return fail("gvss_add_batch_device: not available on a sharded index (the rows live on one GPU): pass host rows to gvss_add_batch");
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     if (x->room.fetch_sub((int64_t)n) < (int64_t)n) {
         x->room.fetch_add((int64_t)n);
         return fail("Reserve capacity ahead of insertions!");
@@ -776,6 +795,7 @@ int gvss_flush(gvss_index *x) {
         }
     }
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     return flush_locked(x);
     API_END
@@ -798,6 +818,7 @@ int gvss_set_build_concurrency(gvss_index *x, uint32_t n) {
     if (!x) return fail("null index");
     if (x->router) return router_set_build_concurrency(x->router, n);
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     x->build_conc = n;
     return 0;
     API_END
@@ -808,6 +829,7 @@ int gvss_remove(gvss_index *x, int64_t key, uint64_t *removed) {
     if (check_usable(x)) return 1;
     if (x->router) return router_remove(x->router, key, removed);
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     if (flush_locked(x)) return 1;
     wait_device_searches(x);
@@ -842,6 +864,7 @@ int gvss_compact(gvss_index *x) {
     if (check_usable(x)) return 1;
     if (x->router) return router_compact(x->router, false, nullptr);
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     if (flush_locked(x)) return 1;
     wait_device_searches(x);
@@ -1248,6 +1271,7 @@ int gvss_load(gvss_index *x, int (*read)(void *, void *, size_t), void *user) {
     if (!x || !read) return fail("gvss_load: null argument");
     if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
     cudaSetDevice(x->device);
     // parsed and uploaded into an index of its own, which changes places with this one only when the whole stream was good
     gvss_config cfg = x->cfg;
@@ -1272,13 +1296,14 @@ int gvss_get_info(gvss_index *x, gvss_info *out) {
     API_BEGIN
     if (!x || !out) return fail("null argument");
     if (x->router) return router_info(x->router, out);
-    std::shared_lock<std::shared_mutex> lk(x->rw);
+    // no lock: the figures are the ones the last writer published (a flush in progress does not make size() / capacity() wait)
     memset(out, 0, sizeof *out);
-    const uint64_t staged = x->staged.load();
-    out->size = x->count - x->n_deleted + staged; // size() counts rows whose add() has returned (SyncSize after the bulk build)
-    out->capacity = x->capacity;
-    out->node_count = x->count + staged;
-    out->max_level = x->max_level < 0 ? 0 : (uint64_t)x->max_level;
+    const uint64_t staged = x->staged.load(), count = x->pub_count.load(), cap = x->pub_capacity.load();
+    out->size = count - x->pub_deleted.load() + staged; // size() counts rows whose add() has returned (SyncSize after the bulk build)
+    out->capacity = cap;
+    out->node_count = count + staged;
+    const int32_t ml = x->pub_max_level.load();
+    out->max_level = ml < 0 ? 0 : (uint64_t)ml;
     out->dimensions = x->cfg.dimensions;
     out->connectivity = x->cfg.connectivity; out->connectivity_base = x->cfg.connectivity_base;
     out->expansion_add = x->cfg.expansion_add; out->expansion_search = x->cfg.expansion_search;
@@ -1289,7 +1314,7 @@ int gvss_get_info(gvss_index *x, gvss_info *out) {
         for (auto &s : x->slots) slot_bytes += s->scratch_bytes + s->io_bytes;
         out->concurrent_searches_peak = x->slots_peak;
     }
-    out->memory_usage = x->capacity * (x->dpad * 4ull + 8 + 2 + x->stride0 * 4ull + 4 + 4) + x->upper_cap * x->strideU * 4ull + x->scratch_bytes + slot_bytes;
+    out->memory_usage = cap * (x->dpad * 4ull + 8 + 2 + x->stride0 * 4ull + 4 + 4) + x->pub_upper_cap.load() * x->strideU * 4ull + x->pub_scratch.load() + slot_bytes;
     return 0;
     API_END
 }
