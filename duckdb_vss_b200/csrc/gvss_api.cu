@@ -135,6 +135,7 @@ struct gvss_index {
     // what gvss_get_info reports, republished by every writer before it lets go of `rw`: size() / capacity() are asked for by
     // HNSWIndex::Construct before every chunk (hnsw_index.cpp:413-431) and must not wait for a flush that holds the writer lock
     std::atomic<uint64_t> pub_capacity{0}, pub_count{0}, pub_deleted{0}, pub_upper_cap{0}, pub_scratch{0};
+    std::atomic<uint64_t> pub_inflight{0}; // rows a flush has taken from staging and not yet published in pub_count
     std::atomic<int32_t> pub_max_level{-1};
 
     // Locking. `rw` plays the role usearch's per-node locks and per-thread contexts play in the reference: searches hold it
@@ -182,8 +183,9 @@ static void recompute_room(gvss_index *x) {
 }
 
 static void publish_info(gvss_index *x) {
-    x->pub_capacity = x->capacity; x->pub_count = x->count; x->pub_deleted = x->n_deleted; x->pub_upper_cap = x->upper_cap;
-    x->pub_scratch = x->scratch_bytes; x->pub_max_level = x->max_level;
+    // order matters to gvss_get_info's lock-free size(): deleted, then count, then the in-flight rows are cleared
+    x->pub_capacity = x->capacity; x->pub_deleted = x->n_deleted; x->pub_count = x->count; x->pub_inflight = 0;
+    x->pub_upper_cap = x->upper_cap; x->pub_scratch = x->scratch_bytes; x->pub_max_level = x->max_level;
 }
 struct Publish { // declared right after a writer lock: runs before the lock is released
     gvss_index *x;
@@ -1298,7 +1300,9 @@ int gvss_get_info(gvss_index *x, gvss_info *out) {
     if (x->router) return router_info(x->router, out);
     // no lock: the figures are the ones the last writer published (a flush in progress does not make size() / capacity() wait)
     memset(out, 0, sizeof *out);
-    const uint64_t staged = x->staged.load(), count = x->pub_count.load(), cap = x->pub_capacity.load();
+    // read order staged -> inflight -> count mirrors the writer's order (inflight set, staged dropped ... count raised, inflight
+    // cleared): during a flush the sum can run ahead by the rows in flight, it never falls behind
+    const uint64_t staged = x->staged.load() + x->pub_inflight.load(), count = x->pub_count.load(), cap = x->pub_capacity.load();
     out->size = count - x->pub_deleted.load() + staged; // size() counts rows whose add() has returned (SyncSize after the bulk build)
     out->capacity = cap;
     out->node_count = count + staged;
@@ -1706,6 +1710,7 @@ static int flush_locked(gvss_index *x) {
     }
     x->level_rng = pl.rng;
     x->upper_used = pl.blocks;
+    x->pub_inflight = n_new; // before staged drops: a lock-free reader may count these rows twice for a moment, never miss them
     x->staged -= n_new;
 
     // (5) device work
