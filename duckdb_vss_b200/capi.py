@@ -78,6 +78,7 @@ SIGNATURES = {
                                                C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gvss_peer_exchange_status": (C.c_int, [C.POINTER(C.c_uint32)]),
     "gvss_set_build_concurrency": (C.c_int, [C.c_void_p, C.c_uint32]),
+    "gvss_set_rows_only": (C.c_int, [C.c_void_p, C.c_int]),
     "gvss_set_background_build": (C.c_int, [C.c_void_p, C.c_uint64]),
     "gvss_last_error": (C.c_char_p, []),
     "gvss_version": (C.c_char_p, []),

@@ -116,6 +116,7 @@ struct gvss_index {
     std::unordered_multimap<int64_t, uint32_t> key_to_slot;
     std::deque<uint32_t> free_slots; // ring of removed slots, FIFO like usearch's free_keys_ (index_dense.hpp:1766-1771)
     uint32_t build_conc = 0;         // gvss_set_build_concurrency
+    bool flat = false;               // gvss_set_rows_only: rows, keys and removals only, no graph is ever built
     uint64_t level_rng = 1;          // minstd_rand0 state (std::default_random_engine, index.hpp:1892)
     std::string poisoned;            // non-empty after a CUDA failure in the middle of a graph update: every later call fails with it
 
@@ -336,8 +337,14 @@ static bool setup_gather4(const gvss_index *x, SearchParams &p) {
 }
 
 // Everything of a search launch that does not depend on where its scratch lives. `grid` = resident query warps wanted.
+// for the calls that read or write adjacency lists
+static int check_graph(const gvss_index *x, const char *what) {
+    if (x->flat) return fail("%s: this index holds rows only (gvss_set_rows_only), it has no graph; gvss_exact_search answers it", what);
+    return 0;
+}
 static int plan_search(const gvss_index *x, const float *d_queries, uint64_t nq, uint32_t k, uint32_t ef, int64_t *d_keys_out,
                        float *d_dist_out, uint32_t *d_counts_out, gvss_search_stats *d_stats_out, SearchParams &p, uint32_t &grid) {
+    if (check_graph(x, "gvss_search")) return 1;
     if (!ef) ef = 64;                        // default_expansion_search, index.hpp:1125,2493-2494
     const uint32_t limit = std::max(ef, k);  // index.hpp:2512
     if (limit > 16384) return fail("gvss: ef/k above 16384 not supported");
@@ -644,6 +651,7 @@ __global__ void k_pack_rows(const float *__restrict__ vectors, uint32_t dpad, ui
 int gvss_compact_rebuild(gvss_index *x, uint64_t *dropped) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (check_graph(x, "gvss_compact_rebuild")) return 1;
     if (x->router) return router_compact(x->router, true, dropped);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     Publish pub{x};
@@ -815,6 +823,18 @@ int gvss_set_background_build(gvss_index *x, uint64_t min_rows) {
     API_END
 }
 
+int gvss_set_rows_only(gvss_index *x, int on) {
+    API_BEGIN
+    if (check_usable(x)) return 1;
+    if (x->router) return fail("gvss_set_rows_only: not available on a sharded index");
+    std::unique_lock<std::shared_mutex> lk(x->rw);
+    Publish pub{x};
+    if (x->count || x->staged.load()) return fail("gvss_set_rows_only: the index already has members; choose before the first add");
+    x->flat = on != 0;
+    return 0;
+    API_END
+}
+
 int gvss_set_build_concurrency(gvss_index *x, uint32_t n) {
     API_BEGIN
     if (!x) return fail("null index");
@@ -864,6 +884,7 @@ int gvss_remove(gvss_index *x, int64_t key, uint64_t *removed) {
 int gvss_compact(gvss_index *x) {
     API_BEGIN
     if (check_usable(x)) return 1;
+    if (check_graph(x, "gvss_compact")) return 1;
     if (x->router) return router_compact(x->router, false, nullptr);
     std::unique_lock<std::shared_mutex> lk(x->rw);
     Publish pub{x};
@@ -1064,6 +1085,7 @@ int gvss_exact_search(gvss_index *x, const float *queries, uint64_t nq, uint32_t
 int gvss_serialized_length(gvss_index *x, uint64_t *bytes) {
     API_BEGIN
     if (check_usable(x) || !bytes) return x && bytes ? 1 : fail("null argument");
+    if (check_graph(x, "gvss_serialized_length")) return 1;
     if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
@@ -1080,6 +1102,7 @@ int gvss_save(gvss_index *x, int (*write)(void *, const void *, size_t), void *u
     API_BEGIN
     if (!x || !write) return fail("gvss_save: null argument");
     if (check_usable(x)) return 1;
+    if (check_graph(x, "gvss_save")) return 1;
     if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     cudaSetDevice(x->device);
     if (flush_if_staged(x)) return 1;
@@ -1271,6 +1294,7 @@ static int load_into(gvss_index *y, int (*read)(void *, void *, size_t), void *u
 int gvss_load(gvss_index *x, int (*read)(void *, void *, size_t), void *user) {
     API_BEGIN
     if (!x || !read) return fail("gvss_load: null argument");
+    if (check_graph(x, "gvss_load")) return 1;
     if (x->router) return fail("a sharded index is not one usearch stream: persisted indexes are single-GPU (the reference cannot merge indexes either, hnsw_index.cpp:561-563)");
     std::unique_lock<std::shared_mutex> lk(x->rw);
     Publish pub{x};
@@ -1540,7 +1564,7 @@ static int flush_device_work(gvss_index *x, const FlushPlan &pl, uint64_t old_co
     uint64_t done = 0;
     const uint64_t total = pl.slots.size(), linked = old_count;
     const int metric = metric_id(x->cfg.metric);
-    while (done < total) {
+    while (done < total && !x->flat) { // a rows-only index stops at the uploads: there is no graph to link the rows into
         const uint64_t have = linked + done;
         uint64_t conc = std::max<uint64_t>(1, have / ramp);
         conc = std::min<uint64_t>(conc, max_warps);
@@ -1668,7 +1692,7 @@ static int flush_locked(gvss_index *x) {
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
     if (!max_warps) { give_back(); return fail("gvss: no CUDA device"); }
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
-    if (ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) return give_back();
+    if (!x->flat && ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) return give_back();
     p.scratch = x->d_scratch;
     // GVSS_BUILD_PROF=1: per-phase SM clocks summed over all inserts, and wall time of the ramp vs the final launch (stderr)
     static const bool prof_on = [] { const char *e = getenv("GVSS_BUILD_PROF"); return e && atoi(e); }();
@@ -1677,7 +1701,7 @@ static int flush_locked(gvss_index *x) {
     p.stats = x->d_build_stats;
     // in-flight registry for the peer pass of k_build (GVSS_BUILD_PEERS=0 disables it)
     static const bool peers_on = [] { const char *e = getenv("GVSS_BUILD_PEERS"); return e ? atoi(e) != 0 : true; }();
-    if (peers_on && inflight_mem.alloc(d_inflight, max_warps) != cudaSuccess) { give_back(); return fail("gvss_flush: out of device memory"); }
+    if (peers_on && !x->flat && inflight_mem.alloc(d_inflight, max_warps) != cudaSuccess) { give_back(); return fail("gvss_flush: out of device memory"); }
     p.inflight = d_inflight;
     if (!pl.host_rows.empty()) { // pinned bounce buffers (slot 0's pinned block, grown to two 16 MB chunks)
         if (x->slots.empty()) { SearchSlot *s = acquire_slot(x); if (!s) return give_back(); release_slot(x, s); }

@@ -65,6 +65,10 @@ class Index:
     def set_build_concurrency(self, n):
         capi.check(capi.lib().gvss_set_build_concurrency(self._h, int(n)))
 
+    def set_rows_only(self, on=True):
+        """Rows, keys and removals only: no graph is built and exact_search is the one search answered (gvss_set_rows_only)."""
+        capi.check(capi.lib().gvss_set_rows_only(self._h, int(bool(on))))
+
     def set_background_build(self, min_rows):
         """Rows staged by add() are inserted by a library thread as soon as ``min_rows`` wait (0 = off)."""
         capi.check(capi.lib().gvss_set_background_build(self._h, int(min_rows)))

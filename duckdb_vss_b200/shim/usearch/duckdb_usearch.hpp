@@ -220,6 +220,10 @@ template <typename key_at = std::int64_t> class index_dense_gt {
         return handle_ && !gvss_search(handle_, queries, nq, (uint32_t)wanted, (uint32_t)ef, (int64_t *)keys, distances, counts, nullptr);
     }
 
+    // rows only, no graph: the transient row store behind the exact join of a table WITHOUT an HNSW index
+    // (integration/n2b_exact_join_unindexed.patch). Only exact_search / exact_search_batch answer afterwards.
+    bool rows_only(bool on = true) { return handle_ && !gvss_set_rows_only(handle_, on ? 1 : 0); }
+
     // exact (brute-force) top-k over the rows the index holds in HBM (integration/n2_exact_mode.patch)
     bool exact_search_batch(const float *queries, std::size_t nq, std::size_t wanted, vector_key_t *keys, float *distances, uint32_t *counts) const {
         return handle_ && !gvss_exact_search(handle_, queries, nq, (uint32_t)wanted, (int64_t *)keys, distances, counts);

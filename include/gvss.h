@@ -121,6 +121,12 @@ int gvss_flush(gvss_index *index);
  * plays in index.reserve({members, threads}) (hnsw_index_physical_create.cpp:296; index_limits_t, index.hpp:1134-1140):
  * with 1 the build is sequential and reproduces the reference's single-thread graph byte for byte. */
 int gvss_set_build_concurrency(gvss_index *index, uint32_t max_concurrent_inserts);
+/* Rows only (SURVEY.md 8(f) N2, tables without an HNSW index): with on != 0 the index keeps rows, keys and removals in HBM
+ * and never builds adjacency lists — gvss_flush stops after the uploads. gvss_exact_search is the one search it answers;
+ * the graph calls (gvss_search*, gvss_save / gvss_load, gvss_compact*) fail with a message. Choose before the first add.
+ * It is the transient row store behind the index join of an un-indexed table (integration/n2b_exact_join_unindexed.patch:
+ * the brute-force lateral join of hnsw_index_macros.cpp:10-78 without the CPU cross product). */
+int gvss_set_rows_only(gvss_index *index, int on);
 /* Pipelined bulk load (the reference collects every row first and builds after Finalize,
  * hnsw_index_physical_create.cpp:98-128,283-306): with min_rows > 0 a library-owned thread uploads and inserts the staged
  * rows whenever at least min_rows of them wait, while the caller goes on adding — table scan, H2D and graph construction

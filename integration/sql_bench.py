@@ -21,9 +21,17 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 
 
-def script(rows, dims, outer, threads, k):
+def script(rows, dims, outer, threads, k, exact_outer=0, gvss=True):
     vec = f"[((hash(i * {dims} + x) % 100000) / 100000.0)::FLOAT for x in range({dims})]::FLOAT[{dims}]"
     const = "[" + ", ".join(f"{((7 * j) % 100) / 100.0:.2f}" for j in range(dims)) + f"]::FLOAT[{dims}]"
+    # N2 for tables WITHOUT an index: the lateral top-k join over the un-indexed table — gvss plans it as HNSW_INDEX_JOIN over a
+    # transient rows-only index (n2b_exact_join_unindexed.patch), the reference runs DuckDB's cross product + window on the CPU
+    unindexed = ""
+    if exact_outer:
+        lateral = f"SELECT count(*), sum(id) FROM q_small, LATERAL (SELECT id FROM t ORDER BY array_distance(t.vec, q_small.qv) LIMIT {k});"
+        unindexed = (f"DROP INDEX idx;\nCREATE TABLE q_small AS SELECT * FROM q WHERE qid < {exact_outer};\n" + ("SET hnsw_exact_search = true;\n" if gvss else "") + ".print ##unindexed_plan\nEXPLAIN " + lateral +
+                     "\n.print ##unindexed_exact_join\n" + lateral +
+                     ("\n.print ##unindexed_exact_join_again\n" + lateral if gvss else "") + "\n.print ##end\n")
     return f"""
 .timer on
 SET threads={threads};
@@ -45,6 +53,7 @@ SELECT count(*), sum(id) FROM q, LATERAL (SELECT id FROM t ORDER BY array_distan
 SELECT count(*), sum(id) FROM q, LATERAL (SELECT id FROM t ORDER BY array_distance(t.vec, q.qv) LIMIT {k});
 .print ##info
 SELECT count, capacity, approx_memory_usage FROM pragma_hnsw_index_info();
+{unindexed}
 """
 
 
@@ -61,7 +70,9 @@ def run(exe, env, sql):
         sections.setdefault(cur, []).append(line)
     times = {name: [float(x) for x in re.findall(r"Run Time \(s\): real ([0-9.]+)", "\n".join(lines))] for name, lines in sections.items()}
     return {"rc": r.returncode, "wall_s": wall, "times_s": times, "index_join_rows": [l for l in sections.get("index_join", []) if "│" in l][-2:],
-            "uses_index_join": "HNSW_INDEX_JOIN" in "\n".join(sections.get("plan", [])), "info": [l for l in sections.get("info", []) if "│" in l][-2:],
+            "uses_index_join": "HNSW_INDEX_JOIN" in "\n".join(sections.get("plan", [])),
+            "unindexed_uses_index_join": "HNSW_INDEX_JOIN" in "\n".join(sections.get("unindexed_plan", [])),
+            "unindexed_rows": [l for l in sections.get("unindexed_exact_join", []) if "│" in l][-2:], "info": [l for l in sections.get("info", []) if "│" in l][-2:],
             "stderr_tail": r.stderr[-500:]}
 
 
@@ -72,9 +83,9 @@ def main():
     ap.add_argument("--outer", type=int, default=4096)
     ap.add_argument("--threads", type=int, default=os.cpu_count() or 8)
     ap.add_argument("--k", type=int, default=10)
+    ap.add_argument("--exact-outer", type=int, default=256, help="outer rows of the exact lateral join on the UN-indexed table (0 = skip)")
     ap.add_argument("--skip-reference", action="store_true")
     args = ap.parse_args()
-    sql = script(args.rows, args.dims, args.outer, args.threads, args.k)
     engines = [("gvss", os.path.join(HERE, "_out", "duckdb"), {"LD_LIBRARY_PATH": f"{HERE}/_out:{ROOT}/duckdb_vss_b200"})]
     ref = os.path.join(ROOT, "oracle", "_ref", "sql", "duckdb_ref")
     if os.path.exists(ref) and not args.skip_reference:
@@ -85,7 +96,7 @@ def main():
             continue
         env = dict(os.environ)
         env.update(extra)
-        res = run(exe, env, sql)
+        res = run(exe, env, script(args.rows, args.dims, args.outer, args.threads, args.k, min(args.exact_outer, args.outer), name == "gvss"))
         t = res["times_s"]
         line = {"engine": name, "rows": args.rows, "dims": args.dims, "outer_rows": args.outer, "k": args.k, "threads": args.threads,
                 "create_index_s": (t.get("create_index") or [None])[0],
@@ -93,6 +104,10 @@ def main():
                 "first_scan_s": (t.get("first_scan") or [None])[0], "scan_s": min(t["scan"]) if t.get("scan") else None,
                 "index_join_s": (t.get("index_join") or [None])[-1], "index_join_again_s": (t.get("index_join_again") or [None])[-1],
                 "index_join_rows_per_s": args.outer / t["index_join_again"][-1] if t.get("index_join_again") and t["index_join_again"][-1] > 0 else None,
+                "unindexed_exact_join_outer_rows": min(args.exact_outer, args.outer),
+                "unindexed_exact_join_s": (t.get("unindexed_exact_join") or [None])[-1],
+                "unindexed_exact_join_again_s": (t.get("unindexed_exact_join_again") or [None])[-1],
+                "unindexed_plan_has_hnsw_index_join": res["unindexed_uses_index_join"], "unindexed_result": res["unindexed_rows"],
                 "plan_has_hnsw_index_join": res["uses_index_join"], "join_result": res["index_join_rows"], "index_info": res["info"],
                 "rc": res["rc"], "stderr_tail": res["stderr_tail"] if res["rc"] else ""}
         print(json.dumps(line), flush=True)

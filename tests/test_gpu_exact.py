@@ -187,3 +187,34 @@ def test_exact_search_over_the_rows_an_index_holds(checker):
         live = ~np.isin(keys, gone)
         want2, _ = gv.exact_topk(metric, base[live], q, k, keys=keys[live])
         np.testing.assert_array_equal(got2, want2)
+
+
+def test_rows_only_index_answers_exact_search_without_a_graph():
+    """gvss_set_rows_only (un-indexed tables): the flush uploads and stops; exact_search equals gvss_exact_topk over the
+    host copy; the graph calls refuse instead of walking empty lists."""
+    n, d, k = 20000, 24, 7
+    base, q = synth.clustered(n, d, 200, 4, 62, 64)
+    keys = np.arange(n, dtype=np.int64) * 2 + 1
+    ix = gv.Index(d, "cosine", M=16)
+    ix.set_rows_only()
+    ix.reserve(n, 2)
+    ix.add_batch(base[:n // 2], keys=keys[:n // 2])
+    ix.flush()
+    ix.add_batch(base[n // 2:], keys=keys[n // 2:])      # second flush appends to the resident rows
+    got_k, got_d, got_c = ix.exact_search(q, k)
+    want_k, want_d = gv.exact_topk("cosine", base, q, k, keys=keys)
+    np.testing.assert_array_equal(got_k, want_k)
+    np.testing.assert_array_equal(got_d.view(np.uint32), want_d.view(np.uint32))
+    assert (got_c == k).all() and ix.size() == n
+    with pytest.raises(gv.GvssError, match="rows only"):
+        ix.ef_search(q, k, 64)
+    with pytest.raises(gv.GvssError, match="rows only"):
+        ix.save()
+    assert ix.remove(int(want_k[0, 0])) == 1
+    got2, _, _ = ix.exact_search(q[:1], k)
+    assert int(want_k[0, 0]) not in got2
+    iy = gv.Index(d, "cosine", M=16)
+    iy.reserve(10, 1)
+    iy.add_batch(base[:10])
+    with pytest.raises(gv.GvssError, match="already has members"):
+        iy.set_rows_only()

@@ -1,6 +1,6 @@
 """CPU: the drop-in claim at compile level. The reference's UNCHANGED extension sources must compile against the gvss shim
-(duckdb_vss_b200/shim ahead of the vendored usearch on the include path), and the two optional operator patches
-(integration/n1_batched_index_join.patch, integration/n3_streaming_sink.patch) must apply to the reference and compile.
+(duckdb_vss_b200/shim ahead of the vendored usearch on the include path), and the optional operator patches
+(integration/n1_*.patch, n2_*.patch, n2b_*.patch, n3_*.patch) must apply to the reference and compile.
 Needs the reference checkout (/root/reference): skipped where it is absent (the GPU box). The linked and SQL-tested
 artefact is integration/build_sql.sh + integration/run_sql_tests.sh (profiles/r3_sql_tests_gpu.log)."""
 import os
@@ -46,6 +46,8 @@ def test_unchanged_extension_sources_compile_against_the_shim():
 @pytest.mark.parametrize("patches,files", [
     (["n1_batched_index_join.patch"], ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
     (["n1_batched_index_join.patch", "n2_exact_mode.patch"], ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
+    (["n1_batched_index_join.patch", "n2_exact_mode.patch", "n2b_exact_join_unindexed.patch"],
+     ["src/hnsw/hnsw_index.cpp", "src/hnsw/hnsw_optimize_join.cpp", "src/include/hnsw/hnsw_index.hpp"]),
     (["n3_streaming_sink.patch"], ["src/hnsw/hnsw_index_physical_create.cpp"]),
 ])
 def test_operator_patches_apply_to_the_reference_and_compile(tmp_path, patches, files):
