@@ -79,6 +79,7 @@ SIGNATURES = {
     "gvss_peer_exchange_status": (C.c_int, [C.POINTER(C.c_uint32)]),
     "gvss_set_build_concurrency": (C.c_int, [C.c_void_p, C.c_uint32]),
     "gvss_set_rows_only": (C.c_int, [C.c_void_p, C.c_int]),
+    "gvss_warmup": (C.c_int, [C.c_int32]),
     "gvss_set_background_build": (C.c_int, [C.c_void_p, C.c_uint64]),
     "gvss_last_error": (C.c_char_p, []),
     "gvss_version": (C.c_char_p, []),

@@ -6,6 +6,7 @@
 #include "router.h"
 
 #include <algorithm>
+#include <chrono>
 #include <atomic>
 #include <condition_variable>
 #include <exception>
@@ -242,6 +243,13 @@ static int16_t draw_level(uint64_t &state, uint32_t M) {
 static int flush_locked(gvss_index *x);
 static int compact_locked(gvss_index *x);
 
+// GVSS_BUILD_PROF=1: milliseconds since the library was first asked, for the host-side timeline printed on stderr
+static const bool g_build_prof = [] { const char *e = getenv("GVSS_BUILD_PROF"); return e && atoi(e); }();
+static double prof_ms() {
+    static const auto t_origin = std::chrono::steady_clock::now();
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_origin).count();
+}
+
 // frees a temporary device allocation on every exit path (the CU() macro returns early)
 struct TempDev {
     void *p = nullptr;
@@ -356,7 +364,7 @@ static int plan_search(const gvss_index *x, const float *d_queries, uint64_t nq,
     static const long long trace = [] { const char *e = getenv("GVSS_TRACE_QUERY"); return e ? atoll(e) : -1ll; }();
     p.trace_query = trace;
     const uint32_t list_cap = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
-    p.sl = make_scratch_layout(limit, x->count, list_cap);
+    p.sl = make_scratch_layout(limit, std::max<uint64_t>(x->count, x->capacity), list_cap); // by capacity: inserts between searches do not regrow it
     p.direct = search_mode_bits();
     const bool g4 = setup_gather4(x, p);
     // Latency kernel (GVSS_SEARCH_LATENCY=0 switches it off): when the whole batch fits the GPU at once even with a 16 KB row
@@ -464,6 +472,7 @@ static int check_usable(const gvss_index *x) {
 // Inserts staged rows if there are any. Takes rw exclusively for that; returns with no lock held.
 static int flush_if_staged(gvss_index *x) {
     if (!x->staged.load()) return 0;
+    if (g_build_prof) fprintf(stderr, "[gvss flush_if_staged] at %.1f ms: %llu rows staged\n", prof_ms(), (unsigned long long)x->staged.load());
     std::unique_lock<std::shared_mutex> lk(x->rw);
     Publish pub{x};
     return flush_locked(x);
@@ -551,10 +560,25 @@ const char *gvss_last_error(void) { return t_error.c_str(); }
 const char *gvss_version(void) { return "gvss 0.2 (sm_100a; usearch v2.12 stream)"; }
 uint64_t gvss_kernel_launches(void) { return g_launches.load(); }
 
+int gvss_warmup(int32_t device) {
+    API_BEGIN
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail("gvss: no CUDA device available (this library has no CPU fallback)");
+    if (device >= ndev) return fail("gvss_warmup: device %d out of range", device);
+    const double t0 = prof_ms();
+    if (device >= 0) CU(cudaSetDevice(device));
+    CU(cudaFree(nullptr)); // creates the primary context: the second or so a first CUDA call costs on a B200
+    if (g_build_prof) fprintf(stderr, "[gvss warmup] device %d: context ready after %.1f ms (started at %.1f ms)\n", device, prof_ms() - t0, t0);
+    return 0;
+    API_END
+}
+
 int gvss_create(const gvss_config *config, gvss_index **out) {
     API_BEGIN
     if (!config || !out) return fail("gvss_create: null argument");
     if (!config->dimensions) return fail("gvss_create: dimensions must be > 0");
+    if (g_build_prof) fprintf(stderr, "[gvss create] at %.1f ms\n", prof_ms());
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return fail("gvss: no CUDA device available (this library has no CPU fallback)");
@@ -719,6 +743,7 @@ int gvss_reserve(gvss_index *x, uint64_t members, uint32_t host_threads) {
     }
     x->level_rng = 1; // reserve() allocates fresh thread contexts => the level sequence restarts (index.hpp:2113,2124)
     wait_device_searches(x);
+    if (g_build_prof) fprintf(stderr, "[gvss reserve] at %.1f ms: %llu members (capacity %llu), %u threads\n", prof_ms(), (unsigned long long)members, (unsigned long long)x->capacity, host_threads);
     return ensure_capacity(x, members);
     API_END
 }
@@ -804,10 +829,13 @@ int gvss_flush(gvss_index *x) {
             return fail("background build failed: %s", why.c_str());
         }
     }
+    if (g_build_prof) fprintf(stderr, "[gvss_flush] called at %.1f ms\n", prof_ms());
     std::unique_lock<std::shared_mutex> lk(x->rw);
     Publish pub{x};
     cudaSetDevice(x->device);
-    return flush_locked(x);
+    const int rc = flush_locked(x);
+    if (g_build_prof) fprintf(stderr, "[gvss_flush] returns at %.1f ms\n", prof_ms());
+    return rc;
     API_END
 }
 
@@ -1608,6 +1636,8 @@ static int flush_device_work(gvss_index *x, const FlushPlan &pl, uint64_t old_co
 static int flush_locked(gvss_index *x) {
     if (check_usable(x)) return 1;
     if (!x->staged.load()) return 0;
+    auto now_ms = [] { return prof_ms(); }; // GVSS_BUILD_PROF: host-side phases of every flush
+    const double t_enter = now_ms();
     wait_device_searches(x);
     const uint32_t d = x->cfg.dimensions;
     struct Taken { std::vector<float> vecs; std::vector<int64_t> keys; };
@@ -1682,7 +1712,8 @@ static int flush_locked(gvss_index *x) {
     p.ef_add = x->cfg.expansion_add;
     const uint32_t cmax = std::max(x->cfg.connectivity_base, x->cfg.connectivity);
     const uint32_t top_cap = std::max(cmax + 1, p.ef_add) + 1;
-    p.sl = make_scratch_layout(std::max(p.ef_add, cmax), pl.next_fresh, cmax);
+    // sized by the capacity, not by the count: a run of flushes into one reservation (the background builder) keeps its scratch
+    p.sl = make_scratch_layout(std::max(p.ef_add, cmax), std::max<uint64_t>(pl.next_fresh, x->capacity), cmax);
     static const uint32_t build_rows = [] { const char *e = getenv("GVSS_BUILD_STAGE_ROWS"); const uint32_t v = e ? (uint32_t)atoi(e) : 32u; return v == 16u ? 16u : 32u; }();
     p.direct = search_mode_bits();
     // with the list-as-queue beam search the heap only serves exact ties: 32 entries (its 5 top levels) stay in shared memory
@@ -1719,6 +1750,7 @@ static int flush_locked(gvss_index *x) {
     }
 
     // (4) commit the host mirrors
+    const double t_planned = now_ms();
     const uint64_t old_count = x->count;
     for (auto &rc : pl.recycled) {
         x->h_keys[rc.first] = rc.second;
@@ -1738,11 +1770,15 @@ static int flush_locked(gvss_index *x) {
     x->staged -= n_new;
 
     // (5) device work
+    const double t_committed = now_ms();
     if (flush_device_work(x, pl, old_count, d_slots, d_inflight, d_prof, max_warps, p)) {
         x->poisoned = t_error;
         cudaGetLastError();
         return 1;
     }
+    if (prof_on)
+        fprintf(stderr, "[gvss flush] entered at %.1f ms: %llu rows; take+plan+alloc %.1f ms, host mirrors %.1f ms, upload+build %.1f ms, left at %.1f ms\n",
+                t_enter, (unsigned long long)n_new, t_planned - t_enter, t_committed - t_planned, now_ms() - t_committed, now_ms());
     return 0;
 }
 

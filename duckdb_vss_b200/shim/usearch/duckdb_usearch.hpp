@@ -26,6 +26,26 @@
 
 #include "gvss.h"
 
+namespace gvss_shim {
+// The first CUDA call of a process creates the context — about a second on a B200, 44 % of a 1M-row CREATE INDEX when it
+// happens inside it. One helper thread starts it when the extension is loaded (static initialisation), joined at exit.
+// GVSS_WARMUP=0 switches it off. Without a GPU gvss_warmup fails at once and nothing else happens.
+struct warmup_at_load_t {
+    std::thread helper;
+    warmup_at_load_t() {
+        const char *e = std::getenv("GVSS_WARMUP");
+        if (e && e[0] == '0') return;
+        helper = std::thread([] { gvss_warmup(-1); });
+    }
+    ~warmup_at_load_t() {
+        if (helper.joinable()) helper.join();
+    }
+};
+// C++11 stand-in for an inline variable: one instance per program, initialised before main once make() below names it
+template <class T = void> struct warmup_holder_t { static warmup_at_load_t instance; };
+template <class T> warmup_at_load_t warmup_holder_t<T>::instance;
+} // namespace gvss_shim
+
 namespace unum {
 namespace usearch {
 
@@ -150,6 +170,7 @@ template <typename key_at = std::int64_t> class index_dense_gt {
 
     // index_dense_gt::make(metric, config) (hnsw_index.cpp:189). A failed creation leaves an index whose calls fail.
     static index_dense_gt make(metric_punned_t metric, index_dense_config_t config = {}) {
+        (void)&gvss_shim::warmup_holder_t<>::instance; // names the start-up helper so that it exists
         index_dense_gt r;
         r.metric_ = metric;
         r.config_ = config;

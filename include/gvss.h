@@ -83,6 +83,11 @@ typedef struct gvss_search_stats {
 
 /* --- lifetime ----------------------------------------------------------------------------------------------- */
 /* index_dense_gt<row_t>::make(metric, config), hnsw_index.cpp:162-189 */
+/* Optional: create the CUDA context of `device` (-1 = the current one) now instead of inside the first gvss_create. On a B200
+ * the first CUDA call of a process costs about a second; a host that knows it will use the index (DuckDB loading the vss
+ * extension) calls this from a helper thread at start-up so that the first CREATE INDEX does not wait for it. Blocking,
+ * idempotent, thread-safe. */
+int gvss_warmup(int32_t device);
 int gvss_create(const gvss_config *config, gvss_index **out);
 /* One logical index partitioned over several GPUs of this process (no counterpart in the reference, which is
  * single-process CPU code): one sub-graph per device, rows dealt out in chunks of 2048 in arrival order, keys stay the
