@@ -517,7 +517,7 @@ static void background_builder(gvss_index *x) {
             if (x->bg_stop) return;
         }
         std::unique_lock<std::shared_mutex> lk(x->rw);
-    Publish pub{x};
+        Publish pub{x};
         if (!x->poisoned.empty()) { x->bg_min_rows = 0; continue; } // nothing more to do for a broken index: go back to sleep
         if (!x->bg_min_rows.load() || x->staged.load() < x->bg_min_rows.load()) continue;
         if (flush_locked(x)) {
