@@ -1678,7 +1678,7 @@ static int flush_locked(gvss_index *x) {
             return s;
         }
         const uint32_t s = (uint32_t)pl.next_fresh++;
-        const int16_t lvl = draw_level(pl.rng, x->cfg.connectivity);
+        const int16_t lvl = x->flat ? (int16_t)0 : draw_level(pl.rng, x->cfg.connectivity); // rows only: no upper lists to size
         pl.fresh_keys.push_back(key);
         pl.fresh_levels.push_back(lvl);
         pl.fresh_off.push_back(lvl > 0 ? (uint32_t)pl.blocks : kInvalid);
