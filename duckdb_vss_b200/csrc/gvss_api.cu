@@ -954,6 +954,8 @@ int gvss_search_device_noalloc(gvss_index *x, const float *queries, uint64_t nq,
     SearchParams p;
     uint32_t resident = 0;
     if (plan_search(x, queries, nq, k, ef, keys_out, dist_out, counts_out, stats_out, p, resident)) return 1;
+    // the built-in scratch is shared out in fixed slots: size them by the members there are, not by the reserved capacity
+    p.sl = make_scratch_layout(p.limit, x->count, std::max(x->cfg.connectivity_base, x->cfg.connectivity));
     char err[384];
     err[0] = 0;
     if (launch_search_static_scratch(metric_id(x->cfg.metric), x->device, view_of(x), p, resident, st, err, sizeof err) != cudaSuccess)
