@@ -1723,6 +1723,11 @@ static int flush_locked(gvss_index *x) {
     p.direct &= ~16; // gather4 staging is a search path
     p.sm = make_smem_layout(x->dpad, top_cap, build_heap, (2 * cmax + 2) * 8, build_rows, true, cmax);
     uint32_t max_warps = resident_warps(x->device, p.sm.bytes, true);
+    if (build_heap == 32u) { // half of those entries go to the overflow area when that lets one more warp per SM in (M=16: 10 -> 11)
+        const SmemLayout tight = make_smem_layout(x->dpad, top_cap, 16u, (2 * cmax + 2) * 8, build_rows, true, cmax);
+        const uint32_t more = resident_warps(x->device, tight.bytes, true);
+        if (more > max_warps) { p.sm = tight; max_warps = more; }
+    }
     if (!max_warps) { give_back(); return fail("gvss: no CUDA device"); }
     if (x->build_conc && x->build_conc < max_warps) max_warps = x->build_conc;
     if (!x->flat && ensure_scratch(x, p.sl.bytes_per_warp * max_warps)) return give_back();
