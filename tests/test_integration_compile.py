@@ -60,3 +60,20 @@ def test_operator_patches_apply_to_the_reference_and_compile(tmp_path, patches, 
     srcs = [str(tmp_path / f) for f in files if f.endswith(".cpp")]
     with ThreadPoolExecutor(max_workers=4) as ex:
         list(ex.map(lambda s: _syntax_check(s, extra_includes=[str(tmp_path / "src" / "include")]), srcs))
+
+
+def test_sql_bench_script_is_well_formed():
+    """integration/sql_bench.py: the generated shell script names every section its parser reads, for both engines (the stock
+    build must not see the hnsw_exact_search setting it does not know)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sql_bench", os.path.join(ROOT, "integration", "sql_bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for gvss in (True, False):
+        sql = mod.script(1000, 8, 64, 4, 10, 16, gvss)
+        for section in ("create_index", "first_scan", "scan", "plan", "index_join", "index_join_again", "info", "unindexed_plan", "unindexed_exact_join"):
+            assert f".print ##{section}\n" in sql, section
+        assert ("hnsw_exact_search" in sql) == gvss
+        assert ("##unindexed_exact_join_again" in sql) == gvss
+        assert sql.index("CREATE INDEX idx") < sql.index("DROP INDEX idx") < sql.index("##unindexed_plan")
+    assert "##unindexed_plan" not in mod.script(1000, 8, 64, 4, 10, 0, True)
